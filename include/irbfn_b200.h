@@ -1,0 +1,169 @@
+/*
+ * irbfn_b200.h -- C ABI of the B200-native IRBFN evaluation library (libirbfn_b200.so).
+ *
+ * This is the drop-in boundary for the one hot path of hzheng40/irbfn: the batched
+ * evaluation (forward + VJP) of the interpolating RBF network.  Every entry point
+ * takes plain device pointers, sizes and a CUDA stream; no torch / XLA / Python types
+ * appear.  An XLA FFI handler, a ctypes binding or a torch extension binds exactly these
+ * symbols (INTEGRATION.md shows each).
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   irbfn_forward          <- WCRBFNet.__call__            src/irbfn_mpc/model.py:169-198
+ *                             (gate  _region_activation     src/irbfn_mpc/model.py:42-95,
+ *                              layer RBFLayer.__call__      flax_rbf/flax_rbf.py:258-285,
+ *                              basis gaussian / inverse_quadratic  flax_rbf.py:34-37,49-52,
+ *                              blend model.py:187-193, readout nn.Dense model.py:196)
+ *   irbfn_forward (hidden) <- DeeperWCRBFNet front end      src/irbfn_mpc/model.py:259-283
+ *   irbfn_forward (gate)   <- ClusterWCRBFNet blend+readout src/irbfn_mpc/model.py:395-414
+ *   irbfn_softmax_gate     <- softmax(Dense(x))             src/irbfn_mpc/model.py:402-406
+ *   irbfn_region_gate      <- _region_activation alone      src/irbfn_mpc/model.py:42-95
+ *   irbfn_backward         <- jax.value_and_grad(loss_fn) through the module,
+ *                             scripts/train_nmpc.py:297,416; scripts/train_nmpc_frenet.py:388,416,448
+ *                             (cotangent dy (B,O) in; dcenters, dlog_sigs, dkernel, dbias,
+ *                              dx, dgate out)
+ *
+ * Conventions
+ *   - All arrays are dense, row-major, fp32 unless stated.  Symbols: B queries, R regions
+ *     (local networks), K kernels per region, D input features, O outputs, S split dims.
+ *   - The library allocates nothing and keeps no global mutable state.  Scratch memory is
+ *     caller-provided (irbfn_*_workspace_bytes tells how much).  Outputs are fully
+ *     overwritten, never accumulated into.
+ *   - All work is enqueued on the given stream; no device-wide synchronisation; every call is
+ *     CUDA-graph capturable.
+ *   - Return value: 0 on success, a negative IRBFN_ERR_* code otherwise.  Nothing is printed
+ *     and nothing aborts.  irbfn_error_string() maps a code to text.
+ *   - x == centre is handled on d^2, so gradients there are the finite analytic limit
+ *     (the reference's sqrt formulation yields NaN).
+ */
+#ifndef IRBFN_B200_H_
+#define IRBFN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IRBFN_ABI_VERSION 1
+
+/* basis functions (flax_rbf.py:34-37, 49-52) */
+#define IRBFN_BASIS_GAUSSIAN 0          /* phi = exp(-alpha^2)     */
+#define IRBFN_BASIS_INVERSE_QUADRATIC 1 /* phi = 1 / (1 + alpha^2) */
+
+/* compiled limits */
+#define IRBFN_MAX_D 8   /* input features               */
+#define IRBFN_MAX_S 8   /* split dimensions of the gate */
+
+/* error codes */
+#define IRBFN_OK 0
+#define IRBFN_ERR_BAD_DIMS (-1)       /* a dimension is <= 0 or inconsistent            */
+#define IRBFN_ERR_UNSUPPORTED_D (-2)  /* D > IRBFN_MAX_D                                */
+#define IRBFN_ERR_BAD_BASIS (-3)      /* basis id is not one of IRBFN_BASIS_*           */
+#define IRBFN_ERR_NULL_POINTER (-4)   /* a required pointer is NULL                     */
+#define IRBFN_ERR_BAD_GATE (-5)       /* neither / both gate inputs, or S > D, S > MAX  */
+#define IRBFN_ERR_WORKSPACE (-6)      /* workspace missing or too small                 */
+#define IRBFN_ERR_LAUNCH (-7)         /* CUDA reported a launch / runtime error         */
+#define IRBFN_ERR_NO_DEVICE (-8)      /* no usable sm_100 device is current             */
+#define IRBFN_ERR_BAD_MASK (-9)       /* grad mask empty or asks for an output whose pointer is NULL */
+
+/* which gradients irbfn_backward produces */
+#define IRBFN_GRAD_CENTERS 0x01u
+#define IRBFN_GRAD_LOG_SIGS 0x02u
+#define IRBFN_GRAD_KERNEL 0x04u /* also produces dbias */
+#define IRBFN_GRAD_X 0x08u
+#define IRBFN_GRAD_GATE 0x10u   /* dgate (B,R); external-gate mode only */
+#define IRBFN_GRAD_PARAMS (IRBFN_GRAD_CENTERS | IRBFN_GRAD_LOG_SIGS | IRBFN_GRAD_KERNEL)
+
+typedef void* irbfn_stream_t; /* a cudaStream_t */
+
+/*
+ * Static description of the tanh region gate (module attributes lower_bounds, upper_bounds,
+ * delta, dimension_ranges, activation_idx of model.py:113-125), packed flat.  The struct lives
+ * on the host; the five arrays live on the device.
+ *   n_d        = offset[d+1] - offset[d] bounds on split dimension d (d < num_split)
+ *   g_d[i](x)  = ((tanh(delta[d]*(x_d - lower[offset[d]+i])) + 1)/2)
+ *              * ((tanh(delta[d]*(upper[offset[d]+i] - x_d)) + 1)/2)
+ *   gamma_r(x) = prod_d g_d[ranges[r*num_split + d]](x)   for r < num_ranges, else 0
+ * Not normalised (model.py:88-93).
+ */
+typedef struct IrbfnGateDesc {
+    int32_t num_split;      /* S = len(activation_idx); split dims are input columns 0..S-1 */
+    int32_t num_ranges;     /* rows of dimension_ranges (normally == R)                      */
+    int32_t num_bounds;     /* sum_d n_d                                                     */
+    const float* lower;     /* device, (num_bounds)                                          */
+    const float* upper;     /* device, (num_bounds)                                          */
+    const int32_t* offset;  /* device, (S + 1)                                               */
+    const float* delta;     /* device, (S)                                                   */
+    const int32_t* ranges;  /* device, (num_ranges, S)                                       */
+} IrbfnGateDesc;
+
+int irbfn_abi_version(void);
+const char* irbfn_error_string(int code);
+
+/*
+ * Forward:  y[b,:] = (sum_r gamma[b,r] * phi(x[b], centers[r], log_sigs[r])) @ W + bias
+ *
+ *   x         (B,D)    queries
+ *   centers   (R,K,D)  params['rbf_list']['centers']
+ *   log_sigs  (R,K)    params['rbf_list']['log_sigs']   (one scalar width per kernel)
+ *   W, bias   (K,O),(O) params['linear']['kernel'|'bias'];  both may be NULL iff y is NULL
+ *   gate      (B,R)    externally computed gate (ClusterWCRBFNet) or NULL
+ *   gd        tanh region gate description or NULL.  Exactly one of gate / gd is given.
+ *   y         (B,O)    output, or NULL
+ *   hidden    (B,K)    blended activations h = sum_r gamma_r phi_r (DeeperWCRBFNet front
+ *                      end, model.py:283), or NULL.  At least one of y / hidden is given.
+ *   workspace / workspace_bytes : >= irbfn_forward_workspace_bytes(...) (may be 0 / NULL).
+ */
+size_t irbfn_forward_workspace_bytes(int64_t B, int R, int K, int D, int O, int fused_gate);
+
+int irbfn_forward(const float* x, const float* centers, const float* log_sigs, const float* W,
+                  const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
+                  float* hidden, int64_t B, int R, int K, int D, int O, int basis,
+                  void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
+
+/*
+ * Backward (VJP).  Recomputes phi from x and the parameters; nothing from the forward is saved.
+ *
+ *   dy        (B,O)    cotangent of y, or NULL (then W may be NULL too)
+ *   dhidden   (B,K)    cotangent of the hidden activations (DeeperWCRBFNet front end), or NULL.
+ *                      At least one of dy / dhidden is given; with both, the cotangent reaching
+ *                      h is dy W^T + dhidden.
+ *   dcenters  (R,K,D)  if grad_mask & IRBFN_GRAD_CENTERS
+ *   dlog_sigs (R,K)    if grad_mask & IRBFN_GRAD_LOG_SIGS
+ *   dW, dbias (K,O),(O) if grad_mask & IRBFN_GRAD_KERNEL
+ *   dx        (B,D)    if grad_mask & IRBFN_GRAD_X.  With a tanh gate (gd) this includes the
+ *                      gate's own dependence on x; with an external gate it is the RBF-layer
+ *                      term only and dgate carries the rest.
+ *   dgate     (B,R)    if grad_mask & IRBFN_GRAD_GATE (external gate only)
+ * Parameter gradients are reduced over the batch deterministically (fixed partition, fixed
+ * order, no atomics).
+ */
+size_t irbfn_backward_workspace_bytes(int64_t B, int R, int K, int D, int O, unsigned grad_mask);
+
+int irbfn_backward(const float* x, const float* centers, const float* log_sigs, const float* W,
+                   const float* gate, const IrbfnGateDesc* gd, const float* dy,
+                   const float* dhidden, float* dcenters, float* dlog_sigs, float* dW, float* dbias,
+                   float* dx, float* dgate, int64_t B, int R, int K, int D, int O, int basis,
+                   unsigned grad_mask, void* workspace, size_t workspace_bytes,
+                   irbfn_stream_t stream);
+
+/* gamma (B,R) of the tanh region gate alone (model.py:42-95). */
+int irbfn_region_gate(const float* x, const IrbfnGateDesc* gd, float* gamma, int64_t B, int R,
+                      int D, irbfn_stream_t stream);
+
+/* ClusterWCRBFNet gate (model.py:402-406): logits = x @ Wc + bc (B,R); gate = softmax(logits).
+ * logits may be NULL. */
+int irbfn_softmax_gate(const float* x, const float* Wc, const float* bc, float* gate,
+                       float* logits, int64_t B, int D, int R, irbfn_stream_t stream);
+
+/* FP32-pipe / XU micro-benchmark used as the roofline denominator (csrc/fp32_peak.cu).
+ * scratch: device, blocks*256 floats. */
+int irbfn_fp32_microbench(int mode, int iters, int blocks, float* scratch,
+                          double* fp32_lane_ops_per_s, double* mufu_lane_ops_per_s,
+                          float* elapsed_ms, irbfn_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IRBFN_B200_H_ */

@@ -1,0 +1,95 @@
+"""ctypes binding of libirbfn_b200.so -- the C ABI declared in include/irbfn_b200.h.
+
+There is no CPU fallback: if the shared library is missing the import of any compute entry
+point raises, and every non-zero return code becomes an ``IrbfnError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libirbfn_b200.so")
+
+BASIS_GAUSSIAN = 0
+BASIS_INVERSE_QUADRATIC = 1
+MAX_D = 8
+MAX_S = 8
+
+GRAD_CENTERS = 0x01
+GRAD_LOG_SIGS = 0x02
+GRAD_KERNEL = 0x04
+GRAD_X = 0x08
+GRAD_GATE = 0x10
+GRAD_PARAMS = GRAD_CENTERS | GRAD_LOG_SIGS | GRAD_KERNEL
+
+ABI_VERSION = 1
+
+# every symbol include/irbfn_b200.h declares (tests check the .so exports exactly these)
+EXPORTED_SYMBOLS = (
+    "irbfn_abi_version", "irbfn_error_string", "irbfn_forward_workspace_bytes", "irbfn_forward",
+    "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
+    "irbfn_softmax_gate", "irbfn_fp32_microbench",
+)
+
+
+class IrbfnError(RuntimeError):
+    def __init__(self, code: int, where: str, text: str):
+        super().__init__("%s failed: %s (code %d)" % (where, text, code))
+        self.code = code
+
+
+class GateDesc(C.Structure):
+    """struct IrbfnGateDesc (include/irbfn_b200.h)."""
+    _fields_ = [
+        ("num_split", C.c_int32), ("num_ranges", C.c_int32), ("num_bounds", C.c_int32),
+        ("lower", C.c_void_p), ("upper", C.c_void_p), ("offset", C.c_void_p),
+        ("delta", C.c_void_p), ("ranges", C.c_void_p),
+    ]
+
+
+_lib = None
+
+
+def load():
+    """dlopen the library (once) and declare the prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "libirbfn_b200.so is not built (%s). Run `python -m irbfn_b200.build`; "
+            "there is no CPU fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    p, i, i64, u, sz = C.c_void_p, C.c_int, C.c_int64, C.c_uint, C.c_size_t
+    lib.irbfn_abi_version.restype = i
+    lib.irbfn_abi_version.argtypes = []
+    lib.irbfn_error_string.restype = C.c_char_p
+    lib.irbfn_error_string.argtypes = [i]
+    lib.irbfn_forward_workspace_bytes.restype = sz
+    lib.irbfn_forward_workspace_bytes.argtypes = [i64, i, i, i, i, i]
+    lib.irbfn_forward.restype = i
+    lib.irbfn_forward.argtypes = [p, p, p, p, p, p, C.POINTER(GateDesc), p, p, i64, i, i, i, i, i,
+                                  p, sz, p]
+    lib.irbfn_backward_workspace_bytes.restype = sz
+    lib.irbfn_backward_workspace_bytes.argtypes = [i64, i, i, i, i, u]
+    lib.irbfn_backward.restype = i
+    lib.irbfn_backward.argtypes = [p, p, p, p, p, C.POINTER(GateDesc), p, p, p, p, p, p, p, p,
+                                   i64, i, i, i, i, i, u, p, sz, p]
+    lib.irbfn_region_gate.restype = i
+    lib.irbfn_region_gate.argtypes = [p, C.POINTER(GateDesc), p, i64, i, i, p]
+    lib.irbfn_softmax_gate.restype = i
+    lib.irbfn_softmax_gate.argtypes = [p, p, p, p, p, i64, i, i, p]
+    lib.irbfn_fp32_microbench.restype = i
+    lib.irbfn_fp32_microbench.argtypes = [i, i, i, p, C.POINTER(C.c_double),
+                                          C.POINTER(C.c_double), C.POINTER(C.c_float), p]
+    if lib.irbfn_abi_version() != ABI_VERSION:
+        raise ImportError("libirbfn_b200.so ABI %d != binding ABI %d"
+                          % (lib.irbfn_abi_version(), ABI_VERSION))
+    _lib = lib
+    return lib
+
+
+def check(code: int, where: str) -> None:
+    if code != 0:
+        raise IrbfnError(code, where, load().irbfn_error_string(code).decode())

@@ -1,0 +1,285 @@
+// C ABI of libirbfn_b200.so (include/irbfn_b200.h): argument validation, launch planning
+// (how parameters are chunked through shared memory) and the two small gate kernels.
+// The heavy kernels live in irbfn_fwd.cuh / irbfn_bwd_x.cuh / irbfn_bwd_p.cuh and are
+// instantiated per feature count in their own translation units.
+#include <cuda_runtime.h>
+
+#include "irbfn_common.cuh"
+#include "irbfn_fwd.cuh"
+#include "irbfn_plan.h"
+
+namespace irbfn {
+int launch_fwd_d4(const FwdArgs&, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d5(const FwdArgs&, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d6(const FwdArgs&, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d7(const FwdArgs&, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d8(const FwdArgs&, int, int, int, size_t, cudaStream_t);
+
+// ---------------------------------------------------------------------------------------
+// device properties, cached per device (immutable after first query; benign race)
+// ---------------------------------------------------------------------------------------
+struct DevInfo {
+    int ok;
+    int sms;
+    int smem_optin;
+    int cc_major;
+};
+
+static int query_device(DevInfo* out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) {
+        cudaGetLastError();
+        return IRBFN_ERR_NO_DEVICE;
+    }
+    static DevInfo cache[64];
+    if (dev < 64 && cache[dev].ok) {
+        *out = cache[dev];
+        return IRBFN_OK;
+    }
+    DevInfo d{};
+    if (cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&d.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) {
+        cudaGetLastError();
+        return IRBFN_ERR_NO_DEVICE;
+    }
+    if (d.cc_major != 10) return IRBFN_ERR_NO_DEVICE;  // sm_100a SASS only
+    d.ok = 1;
+    if (dev < 64) cache[dev] = d;
+    *out = d;
+    return IRBFN_OK;
+}
+
+int device_info(int* sms, int* smem_optin) {
+    DevInfo d;
+    int rc = query_device(&d);
+    if (rc != IRBFN_OK) return rc;
+    *sms = d.sms;
+    *smem_optin = d.smem_optin;
+    return IRBFN_OK;
+}
+
+int check_gate(const float* gate, const IrbfnGateDesc* gd, int D, GateDev* out) {
+    if ((gate == nullptr) == (gd == nullptr)) return IRBFN_ERR_BAD_GATE;
+    *out = GateDev{};
+    if (gd != nullptr) {
+        if (gd->num_split <= 0 || gd->num_split > D || gd->num_split > IRBFN_MAX_S ||
+            gd->num_ranges < 0 || gd->num_bounds <= 0)
+            return IRBFN_ERR_BAD_GATE;
+        if (!gd->lower || !gd->upper || !gd->offset || !gd->delta || !gd->ranges)
+            return IRBFN_ERR_NULL_POINTER;
+        out->S = gd->num_split;
+        out->num_ranges = gd->num_ranges;
+        out->num_bounds = gd->num_bounds;
+        out->lower = gd->lower;
+        out->upper = gd->upper;
+        out->offset = gd->offset;
+        out->delta = gd->delta;
+        out->ranges = gd->ranges;
+    }
+    return IRBFN_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// gamma (B,R) of the tanh region gate alone (model.py:42-95): one thread per query.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) region_gate_kernel(const float* __restrict__ x, GateDev gd,
+                                                          float* __restrict__ gamma, long long B,
+                                                          int R, int D) {
+    extern __shared__ float fac[];  // [256][num_bounds] thread-private rows
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= B) return;
+    float* f = fac + (size_t)threadIdx.x * gd.num_bounds;
+    for (int j = 0; j < gd.S; ++j) {
+        const float xv = __ldg(x + q * D + j);
+        const float k2 = 2.0f * kLog2e * __ldg(gd.delta + j);
+        for (int i = __ldg(gd.offset + j); i < __ldg(gd.offset + j + 1); ++i)
+            f[i] = gate_sigmoid(k2, xv - __ldg(gd.lower + i)) * gate_sigmoid(k2, __ldg(gd.upper + i) - xv);
+    }
+    for (int r = 0; r < R; ++r) {
+        float g = 0.f;
+        if (r < gd.num_ranges) {
+            g = 1.f;
+            for (int j = 0; j < gd.S; ++j)
+                g *= f[__ldg(gd.offset + j) + __ldg(gd.ranges + r * gd.S + j)];
+        }
+        gamma[q * R + r] = g;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// ClusterWCRBFNet gate (model.py:402-406): logits = x Wc + bc ; gate = softmax(logits).
+// One warp per query; lanes stride over the R regions.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) softmax_gate_kernel(const float* __restrict__ x,
+                                                           const float* __restrict__ Wc,
+                                                           const float* __restrict__ bc,
+                                                           float* __restrict__ gate,
+                                                           float* __restrict__ logits, long long B,
+                                                           int D, int R) {
+    const int lane = threadIdx.x & 31;
+    const long long q = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (q >= B) return;
+    float xv[IRBFN_MAX_D];
+#pragma unroll
+    for (int j = 0; j < IRBFN_MAX_D; ++j) xv[j] = j < D ? __ldg(x + q * D + j) : 0.f;
+    float m = -INFINITY;
+    for (int r = lane; r < R; r += 32) {
+        float l = __ldg(bc + r);
+#pragma unroll
+        for (int j = 0; j < IRBFN_MAX_D; ++j)
+            if (j < D) l = fmaf(xv[j], __ldg(Wc + j * R + r), l);
+        gate[q * R + r] = l;  // parked; rewritten below
+        if (logits) logits[q * R + r] = l;
+        m = fmaxf(m, l);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float s = 0.f;
+    for (int r = lane; r < R; r += 32) {
+        const float e = expf(gate[q * R + r] - m);
+        gate[q * R + r] = e;
+        s += e;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float inv = 1.0f / s;
+    for (int r = lane; r < R; r += 32) gate[q * R + r] *= inv;
+}
+
+}  // namespace irbfn
+
+using namespace irbfn;
+
+extern "C" {
+
+int irbfn_abi_version(void) { return IRBFN_ABI_VERSION; }
+
+const char* irbfn_error_string(int code) {
+    switch (code) {
+        case IRBFN_OK: return "ok";
+        case IRBFN_ERR_BAD_DIMS: return "a dimension is <= 0 or inconsistent";
+        case IRBFN_ERR_UNSUPPORTED_D: return "in_features exceeds IRBFN_MAX_D";
+        case IRBFN_ERR_BAD_BASIS: return "unsupported basis function id";
+        case IRBFN_ERR_NULL_POINTER: return "a required pointer is NULL";
+        case IRBFN_ERR_BAD_GATE: return "give exactly one of gate / gate descriptor; 0 < S <= D";
+        case IRBFN_ERR_WORKSPACE: return "workspace missing or too small";
+        case IRBFN_ERR_LAUNCH: return "CUDA launch / runtime error";
+        case IRBFN_ERR_NO_DEVICE: return "no usable sm_100 device is current";
+        case IRBFN_ERR_BAD_MASK: return "gradient mask empty or names an output whose pointer is NULL";
+        default: return "unknown irbfn error code";
+    }
+}
+
+size_t irbfn_forward_workspace_bytes(int64_t, int, int, int, int, int) { return 0; }
+
+int irbfn_forward(const float* x, const float* centers, const float* log_sigs, const float* W,
+                  const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
+                  float* hidden, int64_t B, int R, int K, int D, int O, int basis, void*, size_t,
+                  irbfn_stream_t stream) {
+    if (B < 0 || R <= 0 || K <= 0 || D <= 0) return IRBFN_ERR_BAD_DIMS;
+    if (y != nullptr && O <= 0) return IRBFN_ERR_BAD_DIMS;
+    if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
+    if (basis != IRBFN_BASIS_GAUSSIAN && basis != IRBFN_BASIS_INVERSE_QUADRATIC)
+        return IRBFN_ERR_BAD_BASIS;
+    if (y == nullptr && hidden == nullptr) return IRBFN_ERR_NULL_POINTER;
+    if (!centers || !log_sigs) return IRBFN_ERR_NULL_POINTER;
+    if (y != nullptr && (!W || !bias)) return IRBFN_ERR_NULL_POINTER;
+    GateDev gdev;
+    int rc = check_gate(gate, gd, D, &gdev);
+    if (rc != IRBFN_OK) return rc;
+    if (B == 0) return IRBFN_OK;
+    if (!x) return IRBFN_ERR_NULL_POINTER;
+
+    DevInfo dev;
+    rc = query_device(&dev);
+    if (rc != IRBFN_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+
+    const int DT = D < 4 ? 4 : D;  // compiled feature count; extra columns are zero padding
+    const int Ototal = y ? O : 0;
+    int o0 = 0;
+    bool first = true;
+    // Output windows of at most 16 columns; the hidden activations ride along the first one.
+    do {
+        const int ocur = Ototal - o0 > 16 ? 16 : Ototal - o0;
+        const int OT = fwd_ot_for(ocur);
+        FwdPlan plan;
+        if (!plan_forward(R, K, DT, OT, dev.smem_optin, &plan)) return IRBFN_ERR_BAD_DIMS;
+        FwdArgs a{};
+        a.x = x;
+        a.centers = centers;
+        a.log_sigs = log_sigs;
+        a.W = W;
+        a.bias = bias;
+        a.gate_ext = gate;
+        a.gd = gdev;
+        a.y = ocur > 0 ? y : nullptr;
+        a.hidden = first ? hidden : nullptr;
+        a.B = B;
+        a.R = R;
+        a.K = K;
+        a.Dsrc = D;
+        a.ldw = O;
+        a.o0 = o0;
+        a.ocur = ocur;
+        a.RC = plan.RC;
+        a.KC = plan.KC;
+        a.stage_once = plan.stage_once;
+        const long long tiles = (B + FwdShape::TQ - 1) / FwdShape::TQ;
+        a.num_tiles = (int)tiles;
+        const int grid = (int)(tiles < dev.sms ? tiles : dev.sms);
+        int e;
+        switch (DT) {
+            case 4: e = launch_fwd_d4(a, OT, basis, grid, plan.smem_bytes, st); break;
+            case 5: e = launch_fwd_d5(a, OT, basis, grid, plan.smem_bytes, st); break;
+            case 6: e = launch_fwd_d6(a, OT, basis, grid, plan.smem_bytes, st); break;
+            case 7: e = launch_fwd_d7(a, OT, basis, grid, plan.smem_bytes, st); break;
+            default: e = launch_fwd_d8(a, OT, basis, grid, plan.smem_bytes, st); break;
+        }
+        if (e != 0) return IRBFN_ERR_LAUNCH;
+        o0 += ocur;
+        first = false;
+    } while (o0 < Ototal);
+    return IRBFN_OK;
+}
+
+int irbfn_region_gate(const float* x, const IrbfnGateDesc* gd, float* gamma, int64_t B, int R,
+                      int D, irbfn_stream_t stream) {
+    if (B < 0 || R <= 0 || D <= 0) return IRBFN_ERR_BAD_DIMS;
+    if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
+    GateDev gdev;
+    int rc = check_gate(nullptr, gd, D, &gdev);
+    if (rc != IRBFN_OK) return rc;
+    if (B == 0) return IRBFN_OK;
+    if (!x || !gamma) return IRBFN_ERR_NULL_POINTER;
+    DevInfo dev;
+    rc = query_device(&dev);
+    if (rc != IRBFN_OK) return rc;
+    const size_t smem = (size_t)256 * gdev.num_bounds * sizeof(float);
+    if (smem > (size_t)dev.smem_optin) return IRBFN_ERR_BAD_GATE;
+    if (smem > 48 * 1024 &&
+        cudaFuncSetAttribute(region_gate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)smem) != cudaSuccess)
+        return IRBFN_ERR_LAUNCH;
+    const long long blocks = (B + 255) / 256;
+    region_gate_kernel<<<(unsigned)blocks, 256, smem, (cudaStream_t)stream>>>(x, gdev, gamma, B, R, D);
+    return cudaGetLastError() == cudaSuccess ? IRBFN_OK : IRBFN_ERR_LAUNCH;
+}
+
+int irbfn_softmax_gate(const float* x, const float* Wc, const float* bc, float* gate,
+                       float* logits, int64_t B, int D, int R, irbfn_stream_t stream) {
+    if (B < 0 || R <= 0 || D <= 0) return IRBFN_ERR_BAD_DIMS;
+    if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
+    if (B == 0) return IRBFN_OK;
+    if (!x || !Wc || !bc || !gate) return IRBFN_ERR_NULL_POINTER;
+    DevInfo dev;
+    int rc = query_device(&dev);
+    if (rc != IRBFN_OK) return rc;
+    const long long blocks = (B + 7) / 8;
+    softmax_gate_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, Wc, bc, gate, logits,
+                                                                           B, D, R);
+    return cudaGetLastError() == cudaSuccess ? IRBFN_OK : IRBFN_ERR_LAUNCH;
+}
+
+}  // extern "C"

@@ -1,0 +1,239 @@
+"""Device-level operators: thin wrappers that hand torch CUDA buffers to the C ABI.
+
+torch is used for device memory and streams only; all arithmetic happens in
+libirbfn_b200.so.  Every function requires contiguous fp32 CUDA tensors and raises on
+anything else -- there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_GATE, GRAD_KERNEL,
+                   GRAD_LOG_SIGS, GRAD_PARAMS, GRAD_X)
+
+__all__ = [
+    "GatePack", "forward", "backward", "region_gate", "softmax_gate", "fp32_microbench",
+    "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
+    "GRAD_X", "GRAD_GATE", "GRAD_PARAMS",
+]
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _chk(t: Optional[torch.Tensor], name: str, shape=None, dtype=torch.float32):
+    if t is None:
+        return
+    if not t.is_cuda:
+        raise ValueError("%s must be a CUDA tensor (no CPU fallback)" % name)
+    if t.dtype != dtype:
+        raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
+    if not t.is_contiguous():
+        raise ValueError("%s must be contiguous" % name)
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise ValueError("%s has shape %s, expected %s" % (name, tuple(t.shape), tuple(shape)))
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class GatePack:
+    """The static tanh-gate attributes of a module (lower_bounds, upper_bounds, delta,
+    dimension_ranges; reference model.py:113-125) packed flat on one device, plus the
+    ``IrbfnGateDesc`` that points at them."""
+
+    def __init__(self, lower_bounds: Sequence[Sequence[float]],
+                 upper_bounds: Sequence[Sequence[float]], delta: Sequence[float],
+                 dimension_ranges: Sequence[Sequence[int]], device):
+        S = len(lower_bounds)
+        if S == 0 or len(upper_bounds) != S or len(delta) < S:
+            raise ValueError("lower_bounds, upper_bounds and delta must describe the same split dims")
+        if S > _lib.MAX_S:
+            raise ValueError("at most %d split dimensions are supported" % _lib.MAX_S)
+        offs = [0]
+        for d in range(S):
+            if len(lower_bounds[d]) != len(upper_bounds[d]) or len(lower_bounds[d]) == 0:
+                raise ValueError("bounds of split dim %d are ragged or empty" % d)
+            offs.append(offs[-1] + len(lower_bounds[d]))
+        rng = np.asarray(dimension_ranges, dtype=np.int64).reshape(-1, S) if len(dimension_ranges) \
+            else np.zeros((0, S), np.int64)
+        for d in range(S):
+            if rng.size and (rng[:, d].min() < 0 or rng[:, d].max() >= len(lower_bounds[d])):
+                raise IndexError("dimension_ranges indexes outside the bounds of split dim %d" % d)
+        self.num_split = S
+        self.num_ranges = int(rng.shape[0])
+        self.num_bounds = offs[-1]
+        self.device = torch.device(device)
+        f32 = lambda v: torch.tensor(np.asarray(v, dtype=np.float32), device=self.device)
+        i32 = lambda v: torch.tensor(np.asarray(v, dtype=np.int32), device=self.device)
+        self.lower = f32(np.concatenate([np.asarray(b, np.float64) for b in lower_bounds]))
+        self.upper = f32(np.concatenate([np.asarray(b, np.float64) for b in upper_bounds]))
+        self.offset = i32(offs)
+        self.delta = f32(list(delta)[:S])
+        self.ranges = i32(rng.reshape(-1) if rng.size else np.zeros(1))
+        self.desc = _lib.GateDesc(S, self.num_ranges, self.num_bounds, self.lower.data_ptr(),
+                                  self.upper.data_ptr(), self.offset.data_ptr(),
+                                  self.delta.data_ptr(), self.ranges.data_ptr())
+
+    def ref(self):
+        return C.byref(self.desc)
+
+
+def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: GatePack = None,
+            basis: int = BASIS_GAUSSIAN, want_y: bool = True, want_hidden: bool = False,
+            out=None):
+    """y (B,O) and/or hidden (B,K) of the fused IRBFN forward (irbfn_forward)."""
+    lib = _lib.load()
+    _chk(x, "x")
+    B, D = x.shape
+    _chk(centers, "centers")
+    R, K, Dc = centers.shape
+    if Dc != D:
+        raise ValueError("centers feature count %d != x feature count %d" % (Dc, D))
+    _chk(log_sigs, "log_sigs", (R, K))
+    O = 0
+    y = hidden = None
+    if want_y:
+        _chk(kernel, "kernel")
+        if kernel is None or bias is None:
+            raise ValueError("kernel and bias are required for y")
+        O = kernel.shape[1]
+        _chk(kernel, "kernel", (K, O))
+        _chk(bias, "bias", (O,))
+        y = out if out is not None else torch.empty((B, O), device=x.device, dtype=torch.float32)
+        _chk(y, "out", (B, O))
+    if want_hidden:
+        hidden = torch.empty((B, K), device=x.device, dtype=torch.float32)
+    if gate is not None:
+        _chk(gate, "gate", (B, R))
+    with torch.cuda.device(x.device):
+        rc = lib.irbfn_forward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias),
+                               _ptr(gate), gd.ref() if gd is not None else None, _ptr(y),
+                               _ptr(hidden), B, R, K, D, O, basis, None, 0, _stream())
+    _lib.check(rc, "irbfn_forward")
+    if want_y and want_hidden:
+        return y, hidden
+    return y if want_y else hidden
+
+
+_ws_cache = {}
+
+
+def _workspace(nbytes: int, device) -> Optional[torch.Tensor]:
+    if nbytes == 0:
+        return None
+    key = (torch.device(device), torch.cuda.current_stream(device).cuda_stream)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(nbytes, device=device, dtype=torch.uint8)
+        _ws_cache[key] = ws
+    return ws
+
+
+def backward(x, centers, log_sigs, kernel, dy=None, *, dhidden=None, gate=None,
+             gd: GatePack = None, basis: int = BASIS_GAUSSIAN, grad_mask: int = GRAD_PARAMS,
+             flat_out: Optional[torch.Tensor] = None):
+    """VJP of the forward (irbfn_backward).  Returns a dict with the requested leaves:
+    centers, log_sigs, kernel, bias, x, gate.  If ``flat_out`` is given the parameter
+    gradients are written into that flat buffer in the order [centers, log_sigs, kernel,
+    bias] (the all-reduce payload) and the dict holds views of it."""
+    lib = _lib.load()
+    _chk(x, "x")
+    B, D = x.shape
+    _chk(centers, "centers")
+    R, K, _ = centers.shape
+    _chk(log_sigs, "log_sigs", (R, K))
+    O = 0
+    if dy is not None:
+        _chk(kernel, "kernel")
+        O = kernel.shape[1]
+        _chk(dy, "dy", (B, O))
+    if dhidden is not None:
+        _chk(dhidden, "dhidden", (B, K))
+    if gate is not None:
+        _chk(gate, "gate", (B, R))
+    dev = x.device
+    out = {}
+    sizes = [("centers", GRAD_CENTERS, (R, K, D)), ("log_sigs", GRAD_LOG_SIGS, (R, K)),
+             ("kernel", GRAD_KERNEL, (K, O)), ("bias", GRAD_KERNEL, (O,))]
+    if flat_out is not None:
+        _chk(flat_out, "flat_out")
+        off = 0
+        for name, bit, shp in sizes:
+            if grad_mask & bit:
+                n = int(np.prod(shp))
+                out[name] = flat_out[off:off + n].view(shp)
+                off += n
+        if off > flat_out.numel():
+            raise ValueError("flat_out too small: need %d floats" % off)
+    else:
+        for name, bit, shp in sizes:
+            if grad_mask & bit:
+                out[name] = torch.empty(shp, device=dev, dtype=torch.float32)
+    if grad_mask & GRAD_X:
+        out["x"] = torch.empty((B, D), device=dev, dtype=torch.float32)
+    if grad_mask & GRAD_GATE:
+        out["gate"] = torch.empty((B, R), device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev):
+        nbytes = lib.irbfn_backward_workspace_bytes(B, R, K, D, O, grad_mask)
+        ws = _workspace(nbytes, dev)
+        rc = lib.irbfn_backward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(gate),
+                                gd.ref() if gd is not None else None, _ptr(dy), _ptr(dhidden),
+                                _ptr(out.get("centers")), _ptr(out.get("log_sigs")),
+                                _ptr(out.get("kernel")), _ptr(out.get("bias")), _ptr(out.get("x")),
+                                _ptr(out.get("gate")), B, R, K, D, O, basis, grad_mask, _ptr(ws),
+                                nbytes, _stream())
+    _lib.check(rc, "irbfn_backward")
+    return out
+
+
+def region_gate(x, gd: GatePack, num_regions: int):
+    """gamma (B,R) of the tanh region gate (irbfn_region_gate)."""
+    lib = _lib.load()
+    _chk(x, "x")
+    B, D = x.shape
+    gamma = torch.empty((B, num_regions), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        rc = lib.irbfn_region_gate(_ptr(x), gd.ref(), _ptr(gamma), B, num_regions, D, _stream())
+    _lib.check(rc, "irbfn_region_gate")
+    return gamma
+
+
+def softmax_gate(x, cluster_kernel, cluster_bias, want_logits: bool = True):
+    """(gate, logits) of the ClusterWCRBFNet gate (irbfn_softmax_gate)."""
+    lib = _lib.load()
+    _chk(x, "x")
+    B, D = x.shape
+    R = cluster_kernel.shape[1]
+    _chk(cluster_kernel, "cluster kernel", (D, R))
+    _chk(cluster_bias, "cluster bias", (R,))
+    gate = torch.empty((B, R), device=x.device, dtype=torch.float32)
+    logits = torch.empty((B, R), device=x.device, dtype=torch.float32) if want_logits else None
+    with torch.cuda.device(x.device):
+        rc = lib.irbfn_softmax_gate(_ptr(x), _ptr(cluster_kernel), _ptr(cluster_bias), _ptr(gate),
+                                    _ptr(logits), B, D, R, _stream())
+    _lib.check(rc, "irbfn_softmax_gate")
+    return gate, logits
+
+
+def fp32_microbench(mode: int, iters: int = 20000, blocks: Optional[int] = None, device=None):
+    """FP32-pipe / XU issue-rate micro-benchmark (csrc/fp32_peak.cu).  Returns
+    (fp32 lane-ops/s, MUFU lane-ops/s, elapsed ms)."""
+    lib = _lib.load()
+    device = torch.device(device if device is not None else "cuda")
+    with torch.cuda.device(device):
+        if blocks is None:
+            blocks = torch.cuda.get_device_properties(device).multi_processor_count * 8
+        scratch = torch.empty(blocks * 256, device=device, dtype=torch.float32)
+        f, m, ms = C.c_double(), C.c_double(), C.c_float()
+        rc = lib.irbfn_fp32_microbench(mode, iters, blocks, _ptr(scratch), C.byref(f), C.byref(m),
+                                       C.byref(ms), _stream())
+    _lib.check(rc, "irbfn_fp32_microbench")
+    return f.value, m.value, ms.value
