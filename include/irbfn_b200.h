@@ -100,6 +100,8 @@ typedef struct IrbfnGateDesc {
 
 int irbfn_abi_version(void);
 const char* irbfn_error_string(int code);
+/* After IRBFN_ERR_LAUNCH: which step failed and the CUDA error text.  Per host thread. */
+const char* irbfn_last_error_detail(void);
 
 /*
  * Forward:  y[b,:] = (sum_r gamma[b,r] * phi(x[b], centers[r], log_sigs[r])) @ W + bias

@@ -27,7 +27,7 @@ ABI_VERSION = 1
 
 # every symbol include/irbfn_b200.h declares (tests check the .so exports exactly these)
 EXPORTED_SYMBOLS = (
-    "irbfn_abi_version", "irbfn_error_string", "irbfn_forward_workspace_bytes", "irbfn_forward",
+    "irbfn_abi_version", "irbfn_error_string", "irbfn_last_error_detail", "irbfn_forward_workspace_bytes", "irbfn_forward",
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_fp32_microbench",
 )
@@ -66,6 +66,8 @@ def load():
     lib.irbfn_abi_version.argtypes = []
     lib.irbfn_error_string.restype = C.c_char_p
     lib.irbfn_error_string.argtypes = [i]
+    lib.irbfn_last_error_detail.restype = C.c_char_p
+    lib.irbfn_last_error_detail.argtypes = []
     lib.irbfn_forward_workspace_bytes.restype = sz
     lib.irbfn_forward_workspace_bytes.argtypes = [i64, i, i, i, i, i]
     lib.irbfn_forward.restype = i
@@ -92,4 +94,7 @@ def load():
 
 def check(code: int, where: str) -> None:
     if code != 0:
-        raise IrbfnError(code, where, load().irbfn_error_string(code).decode())
+        text = load().irbfn_error_string(code).decode()
+        if code == -7:
+            text += " [" + load().irbfn_last_error_detail().decode() + "]"
+        raise IrbfnError(code, where, text)

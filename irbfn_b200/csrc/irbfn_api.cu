@@ -3,12 +3,20 @@
 // The heavy kernels live in irbfn_fwd.cuh / irbfn_bwd_x.cuh / irbfn_bwd_p.cuh and are
 // instantiated per feature count in their own translation units.
 #include <cuda_runtime.h>
+#include <stdio.h>
 
 #include "irbfn_common.cuh"
 #include "irbfn_fwd.cuh"
 #include "irbfn_plan.h"
 
 namespace irbfn {
+static thread_local char g_detail[256] = "";
+int note_cuda_error(const char* where, int cuda_error) {
+    snprintf(g_detail, sizeof(g_detail), "%s: %s (cudaError %d)", where,
+             cudaGetErrorString((cudaError_t)cuda_error), cuda_error);
+    cudaGetLastError();  // clear the non-sticky error state
+    return IRBFN_ERR_LAUNCH;
+}
 int launch_fwd_d4(const FwdArgs&, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d5(const FwdArgs&, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d6(const FwdArgs&, int, int, int, size_t, cudaStream_t);
@@ -155,6 +163,8 @@ extern "C" {
 
 int irbfn_abi_version(void) { return IRBFN_ABI_VERSION; }
 
+const char* irbfn_last_error_detail(void) { return g_detail; }
+
 const char* irbfn_error_string(int code) {
     switch (code) {
         case IRBFN_OK: return "ok";
@@ -237,7 +247,7 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
             case 7: e = launch_fwd_d7(a, OT, basis, grid, plan.smem_bytes, st); break;
             default: e = launch_fwd_d8(a, OT, basis, grid, plan.smem_bytes, st); break;
         }
-        if (e != 0) return IRBFN_ERR_LAUNCH;
+        if (e != 0) return note_cuda_error("irbfn_fwd_kernel", e);
         o0 += ocur;
         first = false;
     } while (o0 < Ototal);
@@ -264,7 +274,8 @@ int irbfn_region_gate(const float* x, const IrbfnGateDesc* gd, float* gamma, int
         return IRBFN_ERR_LAUNCH;
     const long long blocks = (B + 255) / 256;
     region_gate_kernel<<<(unsigned)blocks, 256, smem, (cudaStream_t)stream>>>(x, gdev, gamma, B, R, D);
-    return cudaGetLastError() == cudaSuccess ? IRBFN_OK : IRBFN_ERR_LAUNCH;
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? IRBFN_OK : note_cuda_error("region_gate_kernel", (int)e);
 }
 
 int irbfn_softmax_gate(const float* x, const float* Wc, const float* bc, float* gate,
@@ -279,7 +290,8 @@ int irbfn_softmax_gate(const float* x, const float* Wc, const float* bc, float* 
     const long long blocks = (B + 7) / 8;
     softmax_gate_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, Wc, bc, gate, logits,
                                                                            B, D, R);
-    return cudaGetLastError() == cudaSuccess ? IRBFN_OK : IRBFN_ERR_LAUNCH;
+    const cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? IRBFN_OK : note_cuda_error("softmax_gate_kernel", (int)e);
 }
 
 }  // extern "C"

@@ -9,6 +9,10 @@ namespace irbfn {
 
 constexpr float kLog2e = 1.4426950408889634f;
 
+// Diagnostics for IRBFN_ERR_LAUNCH: the failing step and the CUDA error, kept per host thread
+// (irbfn_last_error_detail()).  Defined in irbfn_api.cu.
+int note_cuda_error(const char* where, int cuda_error);  // returns IRBFN_ERR_LAUNCH
+
 // ---- packed fp32 (FFMA2 / FADD2 / FMUL2 on sm_100a: one issue slot, two fp32 lanes) ----
 __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
 __device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }

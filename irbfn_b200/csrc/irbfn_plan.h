@@ -57,4 +57,94 @@ inline bool plan_forward(int R, int K, int D, int OT, int smem_limit, FwdPlan* p
     return false;
 }
 
+// ---------------------------------------------------------------------------------------
+// backward X (query-side): same staging scheme as the forward, wider records, two gate tables
+// ---------------------------------------------------------------------------------------
+inline int bwdx_rec_floats(int D) { return ((2 * D + 4 + 3) / 4) * 4; }
+
+inline size_t bwdx_smem_bytes(int RC, int KC, int D, int OT) {
+    return ((size_t)RC * KC * bwdx_rec_floats(D) + (size_t)KC * 2 * OT + (size_t)2 * RC * kFwdTQ) *
+           sizeof(float);
+}
+
+inline bool plan_bwd_x(int R, int K, int D, int OT, int smem_limit, FwdPlan* p) {
+    const int Kp = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
+    if (bwdx_smem_bytes(R, Kp, D, OT) <= (size_t)smem_limit) {
+        *p = FwdPlan{R, Kp, 1, bwdx_smem_bytes(R, Kp, D, OT)};
+        return true;
+    }
+    const int want = Kp < 64 ? Kp : 64;
+    const int cands[5] = {R < 16 ? R : 16, 8, 4, 2, 1};
+    for (int i = 0; i < 5; ++i) {
+        const int RC = cands[i] < R ? cands[i] : R;
+        if (RC <= 0) continue;
+        const size_t fixed = (size_t)2 * RC * kFwdTQ * sizeof(float);
+        if (fixed >= (size_t)smem_limit) continue;
+        const size_t per_k = ((size_t)RC * bwdx_rec_floats(D) + 2 * OT) * sizeof(float);
+        long long KC = (long long)(((size_t)smem_limit - fixed) / per_k);
+        KC = (KC / kFwdKT) * kFwdKT;
+        if (KC > Kp) KC = Kp;
+        if (KC >= want || (RC == 1 && KC >= kFwdKT)) {
+            *p = FwdPlan{RC, (int)KC, 0, bwdx_smem_bytes(RC, (int)KC, D, OT)};
+            return true;
+        }
+    }
+    return false;
+}
+
+// ---------------------------------------------------------------------------------------
+// backward P (parameter gradients): kernel pairs per thread, chunks of pairs per CTA,
+// query splits, tile size.  Must match irbfn_bwd_p.cuh.
+// ---------------------------------------------------------------------------------------
+inline int bwdp_nkp_for(int OT) { return OT <= 4 ? 3 : (OT <= 10 ? 2 : 1); }
+
+struct BwdPPlan {
+    int OT, NKP, NT;
+    int nchunks, pairs_per_chunk, splits;
+    int TQ, Kspan, Rspan;
+    int PW;              // partial-sum row width: D + 1 + OT
+    size_t smem_bytes;
+    size_t part_floats;  // splits * R*K * PW
+};
+
+inline size_t bwdp_smem_floats(int TQ, int D, int Dsrc, int O, int OT, int Kspan, int Rspan, int has_dhid) {
+    const size_t raw = (size_t)TQ * (Dsrc + O + Rspan + (has_dhid ? Kspan : 0));
+    return 2 * raw + 4 /*align slack*/ + (size_t)TQ * (((2 * D + 3) / 4) * 4) + (size_t)TQ * 2 * (OT > 0 ? OT : 1) +
+           (size_t)TQ * Kspan + (size_t)TQ * (Rspan + 1);
+}
+
+inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT, int has_dhid, int sms,
+                       int smem_limit, BwdPPlan* p) {
+    const long long RK = (long long)R * K;
+    if (RK <= 0 || RK > (1ll << 30)) return false;
+    const int P = (int)((RK + 1) / 2);
+    const int NKP = bwdp_nkp_for(OT);
+    const int per_cta = 256 * NKP;
+    const int nchunks = (P + per_cta - 1) / per_cta;
+    const int Pc = (P + nchunks - 1) / nchunks;
+    int NT = (((Pc + NKP - 1) / NKP + 31) / 32) * 32;
+    if (NT > 256) NT = 256;
+    const long long flen = 2ll * Pc;
+    int Kspan = flen >= K ? K : (int)flen;
+    Kspan = (Kspan + 1) & ~1;
+    int Rspan = (int)((flen + K - 1) / K) + 1;
+    if (Rspan > R) Rspan = R;
+    int TQ = 64;
+    while (TQ >= 4 && bwdp_smem_floats(TQ, D, Dsrc, O, OT, Kspan, Rspan, has_dhid) * sizeof(float) >
+                          (size_t)smem_limit)
+        TQ -= 4;
+    if (TQ < 4) return false;
+    const long long ntiles = (B + TQ - 1) / TQ;
+    long long splits = nchunks <= sms ? sms / nchunks : (4ll * sms + nchunks - 1) / nchunks;
+    if (splits > ntiles) splits = ntiles;
+    if (splits < 1) splits = 1;
+    p->OT = OT; p->NKP = NKP; p->NT = NT;
+    p->nchunks = nchunks; p->pairs_per_chunk = Pc; p->splits = (int)splits;
+    p->TQ = TQ; p->Kspan = Kspan; p->Rspan = Rspan;
+    p->PW = D + 1 + OT;
+    p->smem_bytes = bwdp_smem_floats(TQ, D, Dsrc, O, OT, Kspan, Rspan, has_dhid) * sizeof(float);
+    p->part_floats = (size_t)splits * (size_t)RK * (size_t)p->PW;
+    return true;
+}
+
 }  // namespace irbfn

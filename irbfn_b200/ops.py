@@ -113,6 +113,12 @@ def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: Gate
         hidden = torch.empty((B, K), device=x.device, dtype=torch.float32)
     if gate is not None:
         _chk(gate, "gate", (B, R))
+    if basis not in (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC):
+        _lib.check(-3, "irbfn_forward")
+    if (gate is None) == (gd is None):
+        _lib.check(-5, "irbfn_forward")
+    if B == 0:  # empty tensors have no storage to point at
+        return (y, hidden) if want_y and want_hidden else (y if want_y else hidden)
     with torch.cuda.device(x.device):
         rc = lib.irbfn_forward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias),
                                _ptr(gate), gd.ref() if gd is not None else None, _ptr(y),

@@ -1,0 +1,104 @@
+"""The C-ABI library loads on a machine without a GPU, exports every symbol the header
+declares, and validates arguments before it touches a device (no compute calls here)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+from conftest import ROOT
+from irbfn_b200 import _lib
+
+HEADER = os.path.join(ROOT, "include", "irbfn_b200.h")
+
+
+def _declared_functions():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(irbfn_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_is_built_and_loads():
+    lib = _lib.load()
+    assert lib.irbfn_abi_version() == _lib.ABI_VERSION
+
+
+def test_every_declared_symbol_is_exported():
+    declared = _declared_functions()
+    assert set(declared) == set(_lib.EXPORTED_SYMBOLS)
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True,
+                         check=True).stdout
+    exported = set(re.findall(r" T (irbfn_[a-z0-9_]+)$", out, flags=re.M))
+    assert set(declared) <= exported
+    lib = _lib.load()
+    for name in declared:
+        assert getattr(lib, name) is not None
+
+
+def test_header_constants_match_binding():
+    src = open(HEADER).read()
+    val = lambda name: int(re.search(r"#define\s+%s\s+\(?(-?\w+)\)?" % name, src).group(1).rstrip("u"), 0)
+    assert val("IRBFN_ABI_VERSION") == _lib.ABI_VERSION
+    assert val("IRBFN_BASIS_GAUSSIAN") == _lib.BASIS_GAUSSIAN
+    assert val("IRBFN_BASIS_INVERSE_QUADRATIC") == _lib.BASIS_INVERSE_QUADRATIC
+    assert val("IRBFN_MAX_D") == _lib.MAX_D
+    assert val("IRBFN_GRAD_CENTERS") == _lib.GRAD_CENTERS
+    assert val("IRBFN_GRAD_LOG_SIGS") == _lib.GRAD_LOG_SIGS
+    assert val("IRBFN_GRAD_KERNEL") == _lib.GRAD_KERNEL
+    assert val("IRBFN_GRAD_X") == _lib.GRAD_X
+    assert val("IRBFN_GRAD_GATE") == _lib.GRAD_GATE
+
+
+def test_header_compiles_as_plain_c(tmp_path):
+    src = tmp_path / "t.c"
+    src.write_text('#include "irbfn_b200.h"\nint main(void){IrbfnGateDesc g; (void)g; return IRBFN_OK;}\n')
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                    "-c", str(src), "-o", str(tmp_path / "t.o")], check=True)
+
+
+def test_argument_validation_happens_before_any_device_work():
+    lib = _lib.load()
+    one = C.c_void_p(16)  # never dereferenced: validation fails first
+    fwd = lambda **k: lib.irbfn_forward(one, one, one, one, one, one, None, one, None,
+                                        k.get("B", 4), k.get("R", 2), k.get("K", 3), k.get("D", 4),
+                                        k.get("O", 2), k.get("basis", 0), None, 0, None)
+    assert fwd(R=0) == -1                      # IRBFN_ERR_BAD_DIMS
+    assert fwd(B=-1) == -1
+    assert fwd(D=_lib.MAX_D + 1) == -2         # IRBFN_ERR_UNSUPPORTED_D
+    assert fwd(basis=7) == -3                  # IRBFN_ERR_BAD_BASIS
+    # neither / both gate inputs
+    gd = _lib.GateDesc(1, 1, 1, 16, 16, 16, 16, 16)
+    assert lib.irbfn_forward(one, one, one, one, one, None, None, one, None, 4, 2, 3, 4, 2, 0, None, 0, None) == -5
+    assert lib.irbfn_forward(one, one, one, one, one, one, C.byref(gd), one, None, 4, 2, 3, 4, 2, 0, None, 0, None) == -5
+    # no outputs requested
+    assert lib.irbfn_forward(one, one, one, one, one, one, None, None, None, 4, 2, 3, 4, 2, 0, None, 0, None) == -4
+    # empty batch is a no-op success even without a device
+    assert fwd(B=0) == 0
+    for code in range(0, -10, -1):
+        assert lib.irbfn_error_string(code)
+    assert b"unknown" in lib.irbfn_error_string(-99)
+
+
+def test_backward_argument_validation():
+    lib = _lib.load()
+    one = C.c_void_p(16)
+    bwd = lambda mask, **k: lib.irbfn_backward(
+        one, one, one, one, one, None, one, None, k.get("dC", one), one, one, one, k.get("dx", one), None,
+        k.get("B", 4), k.get("R", 2), 3, k.get("D", 4), 2, 0, mask, None, 0, None)
+    assert bwd(0) == -9                                    # IRBFN_ERR_BAD_MASK: empty
+    assert bwd(_lib.GRAD_CENTERS, dC=None) == -9           # asks for an output with a NULL pointer
+    assert bwd(_lib.GRAD_X, dx=None) == -9
+    assert bwd(_lib.GRAD_PARAMS, R=0) == -1
+    assert bwd(_lib.GRAD_PARAMS, D=9) == -2
+    assert bwd(_lib.GRAD_PARAMS, B=0) == 0
+    assert lib.irbfn_backward_workspace_bytes(1 << 18, 12, 100, 8, 2, _lib.GRAD_PARAMS) > 0
+    # dx alone needs only the (B,R) scratch for d gamma of the tanh gate
+    assert lib.irbfn_backward_workspace_bytes(1 << 18, 12, 100, 8, 2, _lib.GRAD_X) == (1 << 18) * 12 * 4
+
+
+def test_no_cpu_fallback_when_library_missing(monkeypatch, tmp_path):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(ImportError, match="no CPU fallback"):
+        _lib.load()

@@ -1,0 +1,207 @@
+"""GPU parity of the forward (irbfn_forward / irbfn_region_gate / irbfn_softmax_gate, called
+through the C ABI via ctypes) against the oracle and the committed golden fixtures.
+
+Tolerance (BASELINE.json north_star): outputs norm-wise
+max|y - y_ref| / max|y_ref| <= 1e-5 against the float64 reference values.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_paths, load_golden, rel_max
+from oracle import irbfn_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+OUT_TOL = 1e-5
+
+
+def _ops():
+    from irbfn_b200 import ops
+    return ops
+
+
+def _t(a, dev):
+    return torch.tensor(np.ascontiguousarray(a, dtype=np.float32), device=dev)
+
+
+def _gd(cfg, dev):
+    return _ops().GatePack(cfg["lower_bounds"], cfg["upper_bounds"], cfg["delta"],
+                           cfg["dimension_ranges"], dev)
+
+
+@pytest.mark.parametrize("path", golden_paths(), ids=[os.path.basename(p)[:-4] for p in golden_paths()])
+def test_forward_matches_golden(path, cuda_device):
+    ops = _ops()
+    cfg, params, arr = load_golden(path)
+    dev = cuda_device
+    x = _t(arr["x"], dev)
+    rb = params["rbf_list"]
+    basis = orc.BASIS_IDS[cfg["basis_func"]]
+    if cfg["kind"] == "wcrbf":
+        y = ops.forward(x, _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(params["linear"]["kernel"], dev),
+                        _t(params["linear"]["bias"], dev), gd=_gd(cfg, dev), basis=basis)
+    elif cfg["kind"] == "cluster":
+        gate, logits = ops.softmax_gate(x, _t(params["cluster"]["kernel"], dev), _t(params["cluster"]["bias"], dev))
+        assert rel_max(logits.cpu().numpy(), arr["logits64"]) < OUT_TOL
+        y = ops.forward(x, _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(params["linear"]["kernel"], dev),
+                        _t(params["linear"]["bias"], dev), gate=gate, basis=basis)
+    else:  # deeper: hidden activations from the kernel, 64-wide MLP tail in plain fp32 matmuls
+        h = ops.forward(x, _t(rb["centers"], dev), _t(rb["log_sigs"], dev), gd=_gd(cfg, dev), basis=basis,
+                        want_y=False, want_hidden=True)
+        # the kernel's own output: hidden activations against the float64 oracle
+        gamma = orc.region_activation(arr["x"].astype(np.float64), cfg["num_regions"], cfg["lower_bounds"],
+                                      cfg["upper_bounds"], cfg["delta"], cfg["dimension_ranges"])
+        K = rb["centers"].shape[1]
+        _, h_ref = orc.forward(arr["x"].astype(np.float64), rb["centers"], rb["log_sigs"], np.eye(K), np.zeros(K),
+                               gamma, basis, return_hidden=True)
+        assert rel_max(h.cpu().numpy(), h_ref) < OUT_TOL
+        p = {k: {kk: _t(vv, dev) for kk, vv in v.items()} for k, v in params.items() if k != "rbf_list"}
+        h = torch.relu(h @ p["linear_pre1"]["kernel"] + p["linear_pre1"]["bias"])
+        h = torch.relu(h @ p["linear_pre2"]["kernel"] + p["linear_pre2"]["bias"])
+        y = h @ p["linear"]["kernel"] + p["linear"]["bias"]
+        # The shipped 64-wide tail amplifies a 1e-6 perturbation of h to ~2e-3 of y (weights up to
+        # 437), and float32 NumPy evaluation of the whole net is itself 1.5e-5 from float64.  The
+        # tail is plain fp32 matmuls outside the kernel, so the composite gets the adjudication
+        # bound of SURVEY.md 8c (2x the float32 reference's own error, rounded up).
+        assert rel_max(y.cpu().numpy(), arr["y64"]) < 1e-4
+        return
+    assert rel_max(y.cpu().numpy(), arr["y64"]) < OUT_TOL
+
+
+@pytest.mark.parametrize("path", [p for p in golden_paths() if "deeper" not in p and "cluster" not in p][:4])
+def test_region_gate_matches_oracle(path, cuda_device):
+    ops = _ops()
+    cfg, _, arr = load_golden(path)
+    gam = ops.region_gate(_t(arr["x"], cuda_device), _gd(cfg, cuda_device), cfg["num_regions"]).cpu().numpy()
+    ref = orc.region_activation(arr["x"].astype(np.float64), cfg["num_regions"], cfg["lower_bounds"],
+                                cfg["upper_bounds"], cfg["delta"], cfg["dimension_ranges"])
+    assert np.abs(gam - ref).max() < 1e-5
+
+
+def _synthetic(seed, B, R, K, D, O, S=2, nb=(3, 2), num_ranges=None):
+    rng = np.random.default_rng(seed)
+    S = min(S, D)
+    lbs, ubs = [], []
+    for d in range(S):
+        edges = np.linspace(-1.2, 1.2, nb[d % len(nb)] + 1)
+        lbs.append([float(v - 0.05) for v in edges[:-1]])
+        ubs.append([float(v + 0.05) for v in edges[1:]])
+    import itertools
+    combos = list(itertools.product(*[range(len(l)) for l in lbs]))
+    ranges = [list(combos[i % len(combos)]) for i in range(R if num_ranges is None else num_ranges)]
+    cfg = dict(num_regions=R, lower_bounds=lbs, upper_bounds=ubs, delta=[5.0 + 3 * d for d in range(S)],
+               dimension_ranges=ranges, in_features=D, out_features=O, num_kernels=K)
+    p = {"centers": rng.uniform(-1.2, 1.2, (R, K, D)).astype(np.float32),
+         "log_sigs": rng.uniform(-0.7, 0.7, (R, K)).astype(np.float32),
+         "kernel": rng.normal(size=(K, O)).astype(np.float32),
+         "bias": rng.normal(size=O).astype(np.float32)}
+    x = rng.uniform(-1.3, 1.3, (B, D)).astype(np.float32)
+    return cfg, p, x
+
+
+SHAPES = [
+    # B, R, K, D, O
+    (1, 1, 1, 1, 1), (3, 2, 5, 3, 3), (1023, 3, 7, 4, 5), (1025, 6, 10, 5, 7), (5000, 4, 33, 6, 9),
+    (257, 2, 100, 7, 10), (2048, 12, 100, 8, 2), (300, 1, 1000, 8, 16), (200, 3, 9, 8, 18),
+    (129, 2, 6, 2, 40),
+]
+
+
+@pytest.mark.parametrize("basis", [0, 1])
+@pytest.mark.parametrize("shape", SHAPES, ids=["B%d_R%d_K%d_D%d_O%d" % s for s in SHAPES])
+def test_forward_ragged_shapes_match_oracle(shape, basis, cuda_device):
+    ops = _ops()
+    B, R, K, D, O = shape
+    cfg, p, x = _synthetic(11, B, R, K, D, O)
+    dev = cuda_device
+    gamma = orc.region_activation(x.astype(np.float64), R, cfg["lower_bounds"], cfg["upper_bounds"],
+                                  cfg["delta"], cfg["dimension_ranges"])
+    y_ref, h_ref = orc.forward(x, p["centers"], p["log_sigs"], p["kernel"], p["bias"], gamma, basis,
+                               return_hidden=True)
+    y, h = ops.forward(_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev),
+                       _t(p["bias"], dev), gd=_gd(cfg, dev), basis=basis, want_hidden=True)
+    assert rel_max(y.cpu().numpy(), y_ref) < OUT_TOL
+    assert rel_max(h.cpu().numpy(), h_ref) < OUT_TOL
+    # the same through an externally supplied gate
+    y2 = ops.forward(_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev),
+                     _t(p["bias"], dev), gate=_t(gamma, dev), basis=basis)
+    assert rel_max(y2.cpu().numpy(), y_ref) < OUT_TOL
+
+
+def test_forward_parameters_larger_than_shared_memory(cuda_device):
+    """64 x 4096 kernels (the C5 stress shape, 7.6 MB of parameters) are streamed through shared
+    memory in (region, kernel) chunks."""
+    ops = _ops()
+    cfg, p, x = _synthetic(5, 96, 64, 4096, 6, 16, S=3, nb=(4, 4, 4))
+    dev = cuda_device
+    gamma = orc.region_activation(x.astype(np.float64), 64, cfg["lower_bounds"], cfg["upper_bounds"],
+                                  cfg["delta"], cfg["dimension_ranges"])
+    y_ref = orc.forward(x, p["centers"], p["log_sigs"], p["kernel"], p["bias"], gamma, 0, chunk=8)
+    y = ops.forward(_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev),
+                    _t(p["bias"], dev), gd=_gd(cfg, dev), basis=0)
+    assert rel_max(y.cpu().numpy(), y_ref) < OUT_TOL
+
+
+def test_fewer_ranges_than_regions(cuda_device):
+    ops = _ops()
+    cfg, p, x = _synthetic(2, 100, 8, 6, 4, 3, num_ranges=5)
+    dev = cuda_device
+    gamma = orc.region_activation(x.astype(np.float64), 8, cfg["lower_bounds"], cfg["upper_bounds"],
+                                  cfg["delta"], cfg["dimension_ranges"])
+    assert np.all(gamma[:, 5:] == 0)
+    y_ref = orc.forward(x, p["centers"], p["log_sigs"], p["kernel"], p["bias"], gamma, 0)
+    y = ops.forward(_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev),
+                    _t(p["bias"], dev), gd=_gd(cfg, dev), basis=0)
+    assert rel_max(y.cpu().numpy(), y_ref) < OUT_TOL
+
+
+def test_empty_batch_and_errors(cuda_device):
+    ops = _ops()
+    from irbfn_b200._lib import IrbfnError
+    cfg, p, x = _synthetic(2, 4, 2, 3, 4, 2)
+    dev = cuda_device
+    args = (_t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev), _t(p["bias"], dev))
+    y = ops.forward(_t(x[:0], dev), *args, gd=_gd(cfg, dev))
+    assert tuple(y.shape) == (0, 2)
+    with pytest.raises(IrbfnError) as e:
+        ops.forward(_t(x, dev), *args, gd=_gd(cfg, dev), basis=5)
+    assert e.value.code == -3
+    with pytest.raises(IrbfnError):
+        ops.forward(_t(x, dev), *args)  # no gate at all
+    with pytest.raises(ValueError):
+        ops.forward(torch.tensor(x), *args, gd=_gd(cfg, dev))  # CPU tensor: no fallback
+    big = torch.zeros((4, 9), device=dev)
+    with pytest.raises(IrbfnError) as e:
+        ops.forward(big, torch.zeros((2, 3, 9), device=dev), args[1], args[2], args[3], gate=torch.ones((4, 2), device=dev))
+    assert e.value.code == -2
+
+
+def test_forward_is_linear_in_the_readout(cuda_device):
+    """Size-independent property at the full C2 size (2^20 queries): y(W1 + W2, b1 + b2) =
+    y(W1, b1) + y(W2, b2), and doubling the gate doubles h."""
+    ops = _ops()
+    cfg, params, arr = load_golden([p for p in golden_paths() if "c2_frenet_12x100" in p][0])
+    dev = cuda_device
+    rb = params["rbf_list"]
+    B = 1 << 20
+    x = _t(orc.uniform_queries(cfg, B, seed=1), dev)
+    c, ls = _t(rb["centers"], dev), _t(rb["log_sigs"], dev)
+    W1, b1 = _t(params["linear"]["kernel"], dev), _t(params["linear"]["bias"], dev)
+    g = torch.Generator(device="cpu").manual_seed(0)
+    W2 = torch.randn(W1.shape, generator=g).to(dev)
+    b2 = torch.randn(b1.shape, generator=g).to(dev)
+    gd = _gd(cfg, dev)
+    y1 = ops.forward(x, c, ls, W1, b1, gd=gd)
+    y2 = ops.forward(x, c, ls, W2, b2, gd=gd)
+    y12 = ops.forward(x, c, ls, W1 + W2, b1 + b2, gd=gd)
+    scale = y12.abs().max().item()
+    assert (y12 - (y1 + y2)).abs().max().item() / scale < 1e-5
+    # a subsample against the oracle
+    idx = np.arange(0, B, 4099)
+    y_ref = orc.wcrbf_forward(x[idx].cpu().numpy().astype(np.float64), params, cfg)
+    assert rel_max(y1[idx].cpu().numpy(), y_ref) < OUT_TOL
+    # determinism: bit-identical across launches
+    assert torch.equal(y1, ops.forward(x, c, ls, W1, b1, gd=gd))
