@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""bench.py -- IRBFN queries/s on B200 (BASELINE.json metric), one JSON line on stdout.
+
+Workload (config.workload = "C2"): the Frenet-NMPC IRBFN forward over a dense 2^20-point state
+lattice (BASELINE.json configs[1]): module shape R,K,D,O = 12,100,8,2,
+gaussian basis, parameters of scripts/ckpts/dnmpc_12regions_frenet_l1_bigdata/checkpoint_9500
+(carried by tests/golden/c2_frenet_12x100.npz), lattice ey 32 x epsi 32 x vx_car 16 x wz 8 x
+delta 4 x vy_car 2 over the config's bounds, vx_goal and curv held (irbfn_vs_explicit_frenet.ipynb
+cell 8 holds its other dims the same way).
+
+A "step" is one forward pass over the whole lattice.  At N > 1 every rank owns its own 2^20
+lattice (vx_goal differs per rank), no data-path collective: weak scaling.
+
+  value     queries/s, inputs resident in HBM, one kernel launch per step, CUDA-event timed
+  e2e       the same through the public host-buffer call (WCRBFNet.apply on pinned host memory):
+            host->device copy of the queries and device->host copy of the outputs inside the
+            timed region
+  roofline  the kernel is bound by the SM FP32 pipe (arithmetic intensity ~800 flop/byte; see
+            DESIGN.md): achieved = algorithmic FP32-pipe lane-operations / s against the lane-op
+            peak measured in this run by csrc/fp32_peak.cu; the flop and HBM views ride along
+  cpu_baseline  the C/OpenMP float32 oracle (oracle/irbfn_oracle.c) on the host cores
+
+--impl reference times the CPU implementation of the path (the oracle port: JAX, Flax and
+flax_rbf are not installable here) on the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FIXTURE = os.path.join(ROOT, "tests", "golden", "c2_frenet_12x100.npz")
+LATTICE = (("ey", 0, 32), ("epsi", 6, 32), ("vx_car", 2, 16), ("wz", 5, 8), ("delta", 1, 4), ("vy_car", 3, 2))
+B_LATTICE = 1 << 20
+METRIC = "irbfn_forward_queries_per_s"
+UNIT = "queries/s"
+
+
+def load_c2():
+    z = np.load(FIXTURE)
+    cfg = json.loads(str(z["cfg_json"]))
+    p = {"rbf_list": {"centers": z["p/rbf_list/centers"], "log_sigs": z["p/rbf_list/log_sigs"]},
+         "linear": {"kernel": z["p/linear/kernel"], "bias": z["p/linear/bias"]}}
+    return cfg, p
+
+
+def lattice(cfg, vx_goal=4.0, curv=0.0, jitter=0.0):
+    """(2^20, 8) float32: columns (ey, delta, vx_car, vy_car, vx_goal, wz, epsi, curv)."""
+    lo = [min(b) for b in cfg["lower_bounds"]]
+    hi = [max(b) for b in cfg["upper_bounds"]]
+    axes = [np.linspace(lo[c], hi[c], n) + jitter * (hi[c] - lo[c]) / n for _, c, n in LATTICE]
+    grids = np.meshgrid(*axes, indexing="ij")
+    x = np.empty((B_LATTICE, 8), np.float32)
+    x[:, 4] = vx_goal
+    x[:, 7] = curv
+    for (_, c, _), g in zip(LATTICE, grids):
+        x[:, c] = g.reshape(-1)
+    return x
+
+
+def algorithmic_counts(cfg):
+    """Per-query algorithmic work."""
+    R, K, D, O = cfg["num_regions"], cfg["num_kernels"], cfg["in_features"], cfg["out_features"]
+    nb = sum(len(b) for b in cfg["lower_bounds"])
+    S = len(cfg["activation_idx"])
+    flops = R * K * (3 * D + 2) + (2 * K * O + O) + (10 * nb + R * (S - 1))
+    lane_ops = R * K * (2 * D + 2) + K * O          # FP32-pipe thread-instructions, direct form
+    mufu = R * K + 4 * nb
+    hbm_bytes = 4 * (D + O)
+    return dict(flops=flops, lane_ops=lane_ops, mufu=mufu, hbm_bytes=hbm_bytes)
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.samples, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                 "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                 "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def run_reference(args):
+    """CPU arm: the C/OpenMP oracle port on all host cores, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import c_oracle
+    cfg, p = load_c2()
+    sample = 1 << 17
+    x = lattice(cfg)[:: B_LATTICE // sample].copy()
+    cores = c_oracle.num_threads()
+    run = lambda: c_oracle.forward(x, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
+                                   p["linear"]["bias"], 0, cfg=cfg)
+    for _ in range(args.warmup):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        run()
+    dt = (time.perf_counter() - t0) / args.steps
+    v = sample / dt
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C2", "shape": "R12_K100_D8_O2_gaussian", "queries_per_step": sample,
+                   "note": "CPU arm: oracle/irbfn_oracle.c (float32, OpenMP) -- JAX/Flax/flax_rbf are not "
+                           "installable here, so the reference's own JAX CPU path cannot run"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d-point stride sample of the 2^20 lattice per step" % sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the train-step / input-gradient side measurements")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    from irbfn_b200 import ops, parallel
+    from irbfn_b200.basis import gaussian
+    from irbfn_b200.model import WCRBFNet, device_params
+
+    rank, local_rank, world = parallel.init_distributed()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    cfg, p_np = load_c2()
+    net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                   cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"],
+                   cfg["delta"])
+    params = device_params({"params": p_np}, dev)
+    B = B_LATTICE
+    counts = algorithmic_counts(cfg)
+
+    # rotating input sets: 6 x 33.5 MB > 126 MB of L2, so no step finds its queries in cache
+    NSETS = 6
+    xs = [torch.from_numpy(lattice(cfg, vx_goal=4.0 + 0.25 * rank, jitter=0.1 * i)).to(dev) for i in range(NSETS)]
+    ys = [torch.empty((B, cfg["out_features"]), device=dev) for _ in range(NSETS)]
+    p = params["params"]
+    gd = net._gate_pack(dev)
+    fwd = lambda i: ops.forward(xs[i % NSETS], p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"],
+                                p["linear"]["kernel"], p["linear"]["bias"], gd=gd, basis=0, out=ys[i % NSETS])
+
+    def timed(fn, steps, warmup):
+        for i in range(warmup):
+            fn(i)
+        parallel.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        parallel.barrier()
+        return parallel.allreduce_max_scalar(e0.elapsed_time(e1) / steps, dev)
+
+    # ---- device-resident throughput ----
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms = timed(fwd, args.steps, args.warmup)
+    sampler.stop_flag = True
+    sampler.join()
+    value = world * B / (ms * 1e-3)
+
+    # ---- end to end through the public host-buffer call ----
+    xh = torch.from_numpy(lattice(cfg, vx_goal=4.0 + 0.25 * rank)).pin_memory()
+    yh = torch.empty((B, cfg["out_features"]), dtype=torch.float32).pin_memory()
+    ms_e2e = timed(lambda i: net.apply_host(params, xh, out=yh), args.steps, args.warmup)
+    e2e = {"value": world * B / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+           "h2d_bytes_per_step": int(xh.numel() * 4), "d2h_bytes_per_step": int(yh.numel() * 4)}
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C2", "shape": "R12_K100_D8_O2_gaussian", "queries_per_step_per_gpu": B,
+                   "params": "scripts/ckpts/dnmpc_12regions_frenet_l1_bigdata/checkpoint_9500 (tests/golden fixture)",
+                   "l2": "%d rotating input sets (%.0f MB) > 126 MB L2" % (NSETS, NSETS * B * 32 / 1e6),
+                   "parallelism": "dp%d (queries sharded, no collective)" % world},
+        "e2e": e2e, "gpu_launches": args.steps, "clocks": sampler.summary(),
+    }
+
+    if rank == 0:
+        # ---- roofline of irbfn_fwd_kernel (the only kernel of the step) ----
+        peak_lane, _, _ = ops.fp32_microbench(2, iters=20000)    # FADD2+FFMA2: the distance loop's pair
+        peak_ffma, _, _ = ops.fp32_microbench(0, iters=20000)
+        _, peak_mufu, _ = ops.fp32_microbench(3, iters=5000)
+        t = ms * 1e-3
+        ach_lane = counts["lane_ops"] * B / t
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        out["roofline"] = {
+            "bound": "fp32_pipe", "achieved": ach_lane / 1e12, "peak": peak_lane / 1e12, "unit": "T lane-op/s",
+            "frac": ach_lane / peak_lane, "traffic": None,
+            "kernel": "irbfn_fwd_kernel<8,2,gaussian>", "launch_ms": ms,
+            "note": "FP32-pipe lane-operations: R*K*(2D+2) + K*O per query (direct-form distance, scale, blend, "
+                    "readout); peak = FADD2+FFMA2 micro-benchmark measured in this run",
+            "flops": {"achieved_tflops": counts["flops"] * B / t / 1e12, "peak_tflops": 2 * peak_ffma / 1e12,
+                      "frac": counts["flops"] * B / t / (2 * peak_ffma)},
+            "mufu": {"achieved": counts["mufu"] * B / t / 1e12, "peak": peak_mufu / 1e12,
+                     "frac": counts["mufu"] * B / t / peak_mufu, "unit": "T op/s"},
+            "hbm": {"achieved_gbs": counts["hbm_bytes"] * B / t / 1e9, "peak_gbs": hbm_peak,
+                    "frac": counts["hbm_bytes"] * B / t / 1e9 / hbm_peak,
+                    "peak_source": "measured" if "hbm_gbs" in peaks else "fallback"},
+        }
+
+        if not args.no_extras:
+            out["extras"] = extras(net, params, cfg, dev, world, args)
+
+        if world == 1 and not args.no_cpu:
+            from oracle import c_oracle
+            sample = 1 << 18
+            xs_cpu = xs[0][:: B // sample].cpu().numpy().copy()
+            cores = c_oracle.num_threads()
+            run = lambda: c_oracle.forward(xs_cpu, p_np["rbf_list"]["centers"], p_np["rbf_list"]["log_sigs"],
+                                           p_np["linear"]["kernel"], p_np["linear"]["bias"], 0, cfg=cfg)
+            y_cpu = run()
+            t0 = time.perf_counter()
+            reps = 0
+            while reps < 3 or time.perf_counter() - t0 < 10.0:
+                run()
+                reps += 1
+            dt = (time.perf_counter() - t0) / reps
+            y_gpu = ys[0][:: B // sample].cpu().numpy()
+            out["cpu_baseline"] = {"value": sample / dt, "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": "%d-point stride sample of the 2^20 lattice, %d passes of "
+                                             "oracle/irbfn_oracle.c (float32, OpenMP)" % (sample, reps)}
+            out["parity_check"] = {"max_abs_err_over_max_abs": float(np.abs(y_gpu - y_cpu).max() / np.abs(y_cpu).max()),
+                                   "against": "C oracle float32, same %d queries" % sample}
+        print(json.dumps(out))
+    elif not args.no_extras:
+        extras(net, params, cfg, dev, world, args)   # collectives inside: every rank takes part
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+def extras(net, params, cfg, dev, world, args):
+    """Side measurements that explain the headline: the data-parallel training step (C3) and the
+    input-gradient sweep (C4).  Same timing discipline; reported under "extras"."""
+    import torch
+    from irbfn_b200 import ops, parallel
+    from irbfn_b200.train import TrainState, grad_step, train_step
+    rank = parallel.env_world()[0]
+    res = {}
+    p = params["params"]
+    R, K, D, O = cfg["num_regions"], cfg["num_kernels"], cfg["in_features"], cfg["out_features"]
+    lo = np.array([min(b) for b in cfg["lower_bounds"]], np.float32)
+    hi = np.array([max(b) for b in cfg["upper_bounds"]], np.float32)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        parallel.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return parallel.allreduce_max_scalar(e0.elapsed_time(e1) / steps, dev)
+
+    # C3: 262,144 samples per step in total (strong scaling: the global batch is fixed)
+    GB = 262144
+    a, b = parallel.shard_range(GB, rank, world)
+    g = torch.Generator().manual_seed(7)
+    xall = torch.rand((GB, D), generator=g) * torch.from_numpy(hi - lo) + torch.from_numpy(lo)
+    yall = torch.randn((GB, O), generator=g)
+    x, y = xall[a:b].to(dev).contiguous(), yall[a:b].to(dev).contiguous()
+    state = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+    ms_g = timed(lambda: grad_step(state, x, y, GB), args.steps, args.warmup)
+    ms_t = timed(lambda: train_step(state, x, y, GB), args.steps, args.warmup)
+    fl = R * K * (3 * D + 2) + 2 * K * O + R * K * (5 * D + 9) + 4 * K * O
+    res["train_step_C3"] = {"global_batch": GB, "scaling": "strong", "ms_fwd_vjp_allreduce": ms_g,
+                            "ms_with_clip_adam": ms_t, "samples_per_s": GB / (ms_t * 1e-3),
+                            "algorithmic_tflops": fl * GB / (ms_g * 1e-3) / 1e12,
+                            "allreduce_bytes": int(state.grad.numel() * 4)}
+
+    # C4: input gradient for 1M queries per GPU (weak), dx of sum(y)
+    B4 = 1000000
+    x4 = (torch.rand((B4, D), generator=g) * torch.from_numpy(hi - lo) + torch.from_numpy(lo)).to(dev)
+    dy4 = torch.ones((B4, O), device=dev)
+    gd = net._gate_pack(dev)
+    run4 = lambda: ops.backward(x4, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
+                                dy4, gd=gd, basis=0, grad_mask=ops.GRAD_X)
+    ms4 = timed(run4, max(3, args.steps // 2), 3)
+    res["input_grad_C4"] = {"queries_per_gpu": B4, "scaling": "weak", "ms_vjp_dx": ms4,
+                            "queries_per_s": world * B4 / (ms4 * 1e-3),
+                            "algorithmic_tflops": (R * K * (5 * D + 7) + 2 * K * O) * B4 / (ms4 * 1e-3) / 1e12}
+    return res
+
+
+if __name__ == "__main__":
+    main()

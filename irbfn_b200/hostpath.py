@@ -1,0 +1,82 @@
+"""Host-buffer path: queries in host memory in, outputs in host memory out.
+
+The batch is cut into chunks; chunk i's host->device copy, chunk i-1's kernel and chunk i-2's
+device->host copy run concurrently on three CUDA streams ordered by events, out of pinned
+staging memory.  Nothing is computed on the host.  This is the call bench.py's ``e2e`` times.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+
+class HostPipeline:
+    NBUF = 3
+
+    def __init__(self, device, in_features: int, out_features: int, chunk: int = 1 << 17):
+        self.device = torch.device(device)
+        self.D, self.O, self.chunk = in_features, out_features, int(chunk)
+        self.s_in = torch.cuda.Stream(self.device)
+        self.s_run = torch.cuda.Stream(self.device)
+        self.s_out = torch.cuda.Stream(self.device)
+        self.xd = [torch.empty((self.chunk, self.D), device=self.device) for _ in range(self.NBUF)]
+        self.yd = [torch.empty((self.chunk, self.O), device=self.device) for _ in range(self.NBUF)]
+        self.ev_in = [torch.cuda.Event() for _ in range(self.NBUF)]
+        self.ev_run = [torch.cuda.Event() for _ in range(self.NBUF)]
+        self.ev_out = [torch.cuda.Event() for _ in range(self.NBUF)]
+        self._pin_in = None
+        self._pin_out = None
+
+    def _pinned_in(self, x):
+        """x as a pinned fp32 CPU tensor (zero-copy when it already is one)."""
+        if isinstance(x, torch.Tensor) and x.is_pinned() and x.dtype == torch.float32 and x.is_contiguous():
+            return x
+        t = torch.as_tensor(np.ascontiguousarray(np.asarray(x), dtype=np.float32)) if not isinstance(x, torch.Tensor) \
+            else x.float().contiguous()
+        if self._pin_in is None or self._pin_in.shape[0] < t.shape[0]:
+            self._pin_in = torch.empty((t.shape[0], self.D), dtype=torch.float32).pin_memory()
+        buf = self._pin_in[: t.shape[0]]
+        buf.copy_(t)
+        return buf
+
+    def run(self, x, out, launch):
+        """launch(x_dev_chunk, y_dev_chunk) enqueues the kernel on the current stream."""
+        xin = self._pinned_in(x)
+        B = xin.shape[0]
+        if xin.dim() != 2 or xin.shape[1] != self.D:
+            raise ValueError("x must be (B, %d)" % self.D)
+        ret_numpy = out is None
+        if out is None:
+            if self._pin_out is None or self._pin_out.shape[0] < B:
+                self._pin_out = torch.empty((B, self.O), dtype=torch.float32).pin_memory()
+            out = self._pin_out[:B]
+        elif not (isinstance(out, torch.Tensor) and out.is_pinned() and tuple(out.shape) == (B, self.O)):
+            raise ValueError("out must be a pinned CPU tensor of shape (B, %d)" % self.O)
+        cur = torch.cuda.current_stream(self.device)
+        for s in (self.s_in, self.s_run, self.s_out):
+            s.wait_stream(cur)
+        n = (B + self.chunk - 1) // self.chunk
+        for i in range(n):
+            b = i % self.NBUF
+            lo, hi = i * self.chunk, min(B, (i + 1) * self.chunk)
+            m = hi - lo
+            with torch.cuda.stream(self.s_in):
+                if i >= self.NBUF:
+                    self.s_in.wait_event(self.ev_run[b])      # kernel that read xd[b] is done
+                self.xd[b][:m].copy_(xin[lo:hi], non_blocking=True)
+                self.ev_in[b].record(self.s_in)
+            with torch.cuda.stream(self.s_run):
+                self.s_run.wait_event(self.ev_in[b])
+                if i >= self.NBUF:
+                    self.s_run.wait_event(self.ev_out[b])     # copy-out that read yd[b] is done
+                launch(self.xd[b][:m], self.yd[b][:m])
+                self.ev_run[b].record(self.s_run)
+            with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(self.ev_run[b])
+                out[lo:hi].copy_(self.yd[b][:m], non_blocking=True)
+                self.ev_out[b].record(self.s_out)
+        cur.wait_stream(self.s_out)
+        if ret_numpy:
+            cur.synchronize()
+            return out.numpy().copy()
+        return out

@@ -1,0 +1,148 @@
+"""Data-parallel training step for WCRBFNet: forward -> loss cotangent -> hand-written VJP into
+one flat gradient buffer -> all-reduce -> clip_by_global_norm -> Adam.
+
+Mirrors the reference's step (scripts/train_nmpc.py:258-300: ``value_and_grad(loss_fn)`` then
+``state.apply_gradients``; optimiser = ``optax.chain(clip_by_global_norm(g), adam(lr))`` at
+:231-233).  The reference's loss also rolls the prediction through the vehicle dynamics
+(dynamics.py); that term is a "next" row of SURVEY.md 8f and is not part of this step: the
+loss here is the prediction term alone, ``optax.l2_loss(y_pred, y).mean()`` or
+``|y_pred - y|.mean()`` (train_nmpc_frenet.py:402).
+
+Parameters, gradients and both Adam moments live in flat fp32 device buffers laid out
+[centers | log_sigs | kernel | bias]; the leaves of the params tree are views, so the whole
+update is a handful of element-wise launches over one buffer and the all-reduce is one call.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import ops, parallel
+from .model import WCRBFNet, _leaf, _unwrap
+
+
+class TrainState:
+    """step / params / opt_state holder (the reference's flax TrainState, scripts/train_nmpc.py:236)."""
+
+    def __init__(self, module: WCRBFNet, params: dict, lr: float, max_grad_norm: float = 1.0,
+                 b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, device=None):
+        if not isinstance(module, WCRBFNet):
+            raise TypeError("TrainState drives WCRBFNet (the shape train_nmpc*.py trains)")
+        p = _unwrap(params)
+        device = torch.device(device) if device is not None else _leaf_device(p)
+        self.module = module
+        self.apply_fn = module.apply
+        self.lr, self.max_grad_norm, self.b1, self.b2, self.eps = lr, max_grad_norm, b1, b2, eps
+        self.step = 0
+        R, K, D, O = module.num_regions, module.num_kernels, module.in_features, module.out_features
+        rb = p.get("rbf_list", {})
+        self.train_centers = "centers" in rb
+        self.train_log_sigs = "log_sigs" in rb
+        shapes = []
+        if self.train_centers:
+            shapes.append(("centers", (R, K, D)))
+        if self.train_log_sigs:
+            shapes.append(("log_sigs", (R, K)))
+        shapes += [("kernel", (K, O)), ("bias", (O,))]
+        n = sum(int(np.prod(s)) for _, s in shapes)
+        self.flat = torch.empty(n, device=device, dtype=torch.float32)
+        self.grad = torch.zeros_like(self.flat)
+        self.mu = torch.zeros_like(self.flat)
+        self.nu = torch.zeros_like(self.flat)
+        self.views, self.gviews = {}, {}
+        off = 0
+        for name, shp in shapes:
+            m = int(np.prod(shp))
+            self.views[name] = self.flat[off:off + m].view(shp)
+            self.gviews[name] = self.grad[off:off + m].view(shp)
+            off += m
+        src = {"centers": rb.get("centers"), "log_sigs": rb.get("log_sigs"),
+               "kernel": p["linear"]["kernel"], "bias": p["linear"]["bias"]}
+        for name in self.views:
+            self.views[name].copy_(_leaf(src[name], device))
+        self.mask = (ops.GRAD_CENTERS if self.train_centers else 0) | \
+                    (ops.GRAD_LOG_SIGS if self.train_log_sigs else 0) | ops.GRAD_KERNEL
+        self.device = device
+
+    @property
+    def params(self) -> dict:
+        rb = {k: self.views[k] for k in ("centers", "log_sigs") if k in self.views}
+        p = {"linear": {"kernel": self.views["kernel"], "bias": self.views["bias"]}}
+        if rb:
+            p["rbf_list"] = rb
+        return {"params": p}
+
+    def opt_state(self) -> dict:
+        return {"count": self.step, "mu": self.mu, "nu": self.nu}
+
+
+def _leaf_device(p):
+    for v in p.values():
+        if isinstance(v, dict):
+            d = _leaf_device(v)
+            if d is not None:
+                return d
+        elif isinstance(v, torch.Tensor) and v.is_cuda:
+            return v.device
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def loss_and_cotangent(y_pred: torch.Tensor, y: torch.Tensor, global_batch: int, loss: str = "l2"):
+    """(sum of this shard's loss terms / global element count, dL/dy_pred) for the mean over
+    the GLOBAL batch, so that summing shard gradients over ranks gives the one-device gradient."""
+    n = float(global_batch * y.shape[1])
+    diff = y_pred - y
+    if loss == "l2":      # optax.l2_loss = 0.5 * (pred - target)^2
+        return 0.5 * (diff * diff).sum() / n, diff / n
+    if loss == "l1":
+        return diff.abs().sum() / n, torch.sign(diff) / n
+    raise ValueError("loss must be 'l2' or 'l1'")
+
+
+def clip_and_adam_(state: TrainState):
+    """optax.chain(clip_by_global_norm(max_norm), adam(lr)) on the flat buffers, in place."""
+    g = state.grad
+    gnorm = torch.linalg.vector_norm(g)
+    scale = torch.clamp(state.max_grad_norm / torch.clamp(gnorm, min=1e-30), max=1.0)  # optax: g * min(1, c/|g|)
+    g.mul_(scale)
+    state.step += 1
+    state.mu.mul_(state.b1).add_(g, alpha=1 - state.b1)
+    state.nu.mul_(state.b2).addcmul_(g, g, value=1 - state.b2)
+    bc1 = 1 - state.b1 ** state.step
+    bc2 = 1 - state.b2 ** state.step
+    state.flat.addcdiv_(state.mu / bc1, (state.nu / bc2).sqrt_().add_(state.eps), value=-state.lr)
+    return gnorm
+
+
+def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch: Optional[int] = None,
+              loss: str = "l2"):
+    """Forward + VJP on this rank's shard, then the gradient all-reduce.  Leaves the reduced
+    gradient in ``state.grad`` and returns the (global) loss as a device scalar."""
+    m = state.module
+    dev = x.device
+    centers, log_sigs = m._rbf_leaves(_unwrap(state.params), dev)
+    v = state.views
+    gd = m._gate_pack(dev)
+    gb = int(global_batch) if global_batch is not None else int(x.shape[0])
+    y_pred = ops.forward(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis)
+    lval, dy = loss_and_cotangent(y_pred, y, gb, loss)
+    ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gd=gd, basis=m._basis,
+                 grad_mask=state.mask, flat_out=state.grad)
+    if gb != x.shape[0]:
+        buf = torch.cat([state.grad, lval.reshape(1)])   # loss rides along: still one collective
+        parallel.allreduce_sum_(buf)
+        state.grad.copy_(buf[:-1])
+        lval = buf[-1]
+    return lval
+
+
+def train_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch: Optional[int] = None,
+               loss: str = "l2"):
+    """One optimiser step (scripts/train_nmpc.py:258-300 without the dynamics term).  ``x``/``y``
+    are this rank's shard; ``global_batch`` the total over ranks.  Returns the loss (device scalar;
+    no host sync -- the reference's per-step wandb device_get is the caller's business)."""
+    lval = grad_step(state, x, y, global_batch, loss)
+    clip_and_adam_(state)
+    return lval
