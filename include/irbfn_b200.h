@@ -160,9 +160,15 @@ int irbfn_softmax_gate(const float* x, const float* Wc, const float* bc, float* 
                        float* logits, int64_t B, int D, int R, irbfn_stream_t stream);
 
 /* FP32-pipe / XU micro-benchmark used as the roofline denominator (csrc/fp32_peak.cu).
- * scratch: device, blocks*256 floats. */
+ * scratch: device, blocks*512 floats. */
 int irbfn_fp32_microbench(int mode, int iters, int blocks, float* scratch,
                           double* fp32_lane_ops_per_s, double* mufu_lane_ops_per_s,
+                          float* elapsed_ms, irbfn_stream_t stream);
+
+/* Same benchmark, all pipes: rates[0] = FP32-pipe, rates[1] = MUFU (XU), rates[2] = FP64-pipe
+ * lane-operations per second.  Modes 0-6 as above; 7-56 are the FP32/FP64 co-issue, DMMA and
+ * warp-specialisation probes documented at the top of csrc/fp32_peak.cu. */
+int irbfn_pipe_microbench(int mode, int iters, int blocks, float* scratch, double* rates,
                           float* elapsed_ms, irbfn_stream_t stream);
 
 #ifdef __cplusplus

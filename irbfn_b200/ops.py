@@ -17,7 +17,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
                    GRAD_LOG_SIGS, GRAD_PARAMS, GRAD_X)
 
 __all__ = [
-    "GatePack", "forward", "backward", "region_gate", "softmax_gate", "fp32_microbench",
+    "GatePack", "forward", "backward", "region_gate", "softmax_gate", "fp32_microbench", "pipe_microbench",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
     "GRAD_X", "GRAD_GATE", "GRAD_PARAMS",
 ]
@@ -237,9 +237,23 @@ def fp32_microbench(mode: int, iters: int = 20000, blocks: Optional[int] = None,
     with torch.cuda.device(device):
         if blocks is None:
             blocks = torch.cuda.get_device_properties(device).multi_processor_count * 8
-        scratch = torch.empty(blocks * 256, device=device, dtype=torch.float32)
+        scratch = torch.empty(blocks * 512, device=device, dtype=torch.float32)
         f, m, ms = C.c_double(), C.c_double(), C.c_float()
         rc = lib.irbfn_fp32_microbench(mode, iters, blocks, _ptr(scratch), C.byref(f), C.byref(m),
                                        C.byref(ms), _stream())
     _lib.check(rc, "irbfn_fp32_microbench")
     return f.value, m.value, ms.value
+
+
+def pipe_microbench(mode: int, iters: int = 20000, blocks: Optional[int] = None, device=None):
+    """All-pipe variant (irbfn_pipe_microbench): (fp32, MUFU, fp64 lane-ops/s, elapsed ms)."""
+    lib = _lib.load()
+    device = torch.device(device if device is not None else "cuda")
+    with torch.cuda.device(device):
+        if blocks is None:
+            blocks = torch.cuda.get_device_properties(device).multi_processor_count * 8
+        scratch = torch.empty(blocks * 512, device=device, dtype=torch.float32)
+        rates, ms = (C.c_double * 3)(), C.c_float()
+        rc = lib.irbfn_pipe_microbench(mode, iters, blocks, _ptr(scratch), rates, C.byref(ms), _stream())
+    _lib.check(rc, "irbfn_pipe_microbench")
+    return rates[0], rates[1], rates[2], ms.value
