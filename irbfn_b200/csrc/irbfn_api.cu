@@ -17,11 +17,11 @@ int note_cuda_error(const char* where, int cuda_error) {
     cudaGetLastError();  // clear the non-sticky error state
     return IRBFN_ERR_LAUNCH;
 }
-int launch_fwd_d4(const FwdArgs&, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d5(const FwdArgs&, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d6(const FwdArgs&, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d7(const FwdArgs&, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d8(const FwdArgs&, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d4(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d5(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d6(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d7(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwd_d8(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 
 // ---------------------------------------------------------------------------------------
 // device properties, cached per device (immutable after first query; benign race)
@@ -236,16 +236,17 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
         a.RC = plan.RC;
         a.KC = plan.KC;
         a.stage_once = plan.stage_once;
-        const long long tiles = (B + FwdShape::TQ - 1) / FwdShape::TQ;
+        const long long tq = (long long)plan.NT * FwdShape::Q;
+        const long long tiles = (B + tq - 1) / tq;
         a.num_tiles = (int)tiles;
         const int grid = (int)(tiles < dev.sms ? tiles : dev.sms);
         int e;
         switch (DT) {
-            case 4: e = launch_fwd_d4(a, OT, basis, grid, plan.smem_bytes, st); break;
-            case 5: e = launch_fwd_d5(a, OT, basis, grid, plan.smem_bytes, st); break;
-            case 6: e = launch_fwd_d6(a, OT, basis, grid, plan.smem_bytes, st); break;
-            case 7: e = launch_fwd_d7(a, OT, basis, grid, plan.smem_bytes, st); break;
-            default: e = launch_fwd_d8(a, OT, basis, grid, plan.smem_bytes, st); break;
+            case 4: e = launch_fwd_d4(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            case 5: e = launch_fwd_d5(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            case 6: e = launch_fwd_d6(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            case 7: e = launch_fwd_d7(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            default: e = launch_fwd_d8(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
         }
         if (e != 0) return note_cuda_error("irbfn_fwd_kernel", e);
         o0 += ocur;

@@ -4,44 +4,49 @@
 //   gate    src/irbfn_mpc/model.py:70-95      blend   src/irbfn_mpc/model.py:187-193
 //   layer   flax_rbf/flax_rbf.py:275-283      readout src/irbfn_mpc/model.py:196
 //
-// Design ("forward kernel"):
+// Design:
 //   * query-stationary: each thread owns Q = 4 queries, held in registers as two packed pairs
-//     (x_{q0,j}, x_{q1,j}); every fp32 operation of the distance loop is a packed FADD2/FFMA2,
-//     so an (query, region, kernel) evaluation costs D+2 issue slots for 2D+2 FP32-pipe cycles
-//     and the kernel is bound by the FP32 pipe, not by instruction issue.
+//     (x_{q0,j}, x_{q1,j}); every fp32 operation of the distance loop is a packed FADD2/FFMA2
+//     whose centre operand is a scalar register broadcast to both lanes (SASS `Rn.F32`), so a
+//     (query, region, kernel) evaluation costs D+2 issue slots for 2D+2 FP32-pipe cycles and the
+//     kernel is bound by the FP32 pipe, not by instruction issue.
 //   * parameters are staged in shared memory once per block (or once per (region,kernel) chunk
-//     when they do not fit) as records  [-c_0,-c_0, ..., -c_{D-1},-c_{D-1}, s, s, pad]  so a
-//     broadcast LDS.128 delivers two ready-made packed operands; s already contains
-//     exp(-2 log_sig) (times -log2 e for the gaussian), so the hot loop has no divide / sqrt.
-//   * the gate lives in a thread-private column of a shared-memory table gtab[region][query],
+//     when they do not fit) as tiles of KT = 4 kernels, TRANSPOSED: row j of a tile holds -c_j of
+//     its four kernels, row D their width scales s = exp(-2 log_sig) (times -log2 e for the
+//     gaussian).  One broadcast LDS.128 per feature feeds 8 independent packed chains
+//     (4 kernels x 2 query pairs): feature-outer, chain-inner, so latency hides inside one warp.
+//   * the gate lives in a thread-private column of a shared-memory table gtab[region][thread],
 //     computed once per query tile from the packed bound tables (no (B,R) array in HBM).
-//   * loop order: kernel tile (KT=4) outer, region inner, so the blended activation h_k is
-//     complete in registers before the readout touches it; (B,R,K) and (B,K) never exist.
-//   * persistent grid: one 256-thread CTA per SM walks query tiles of 1024 queries.
+//   * loop order: kernel tile outer, region inner, so the blended activation h_k is complete in
+//     registers before the readout touches it; (B,R,K) and (B,K) never exist.  The basis function
+//     (MUFU) of one (tile, region) step is evaluated DURING the next step, two MUFUs after each
+//     feature of its distance loop, and blended at that step's end (software pipeline): the XU
+//     never sees a burst and its latency is covered by packed arithmetic of the same warp.
+//   * persistent grid: one NT-thread CTA per SM walks query tiles of NT*4 queries.
 #pragma once
 #include "irbfn_common.cuh"
 
 namespace irbfn {
 
 struct FwdShape {
-    static constexpr int NT = 256;        // threads per CTA
     static constexpr int Q = 4;           // queries per thread
-    static constexpr int TQ = NT * Q;     // queries per CTA tile
-    static constexpr int KT = 4;          // kernels per register tile
-    static __host__ __device__ constexpr int rec_floats(int D) { return ((2 * D + 2 + 3) / 4) * 4; }
+    static constexpr int KT = 4;          // kernels per register tile / per shared-memory tile
+    static __host__ __device__ constexpr int tile_floats(int D) { return (D + 1) * 4; }
 };
 
-template <int D, int OT, int BASIS>
-__global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
-    constexpr int NT = FwdShape::NT, Q = FwdShape::Q, TQ = FwdShape::TQ, KT = FwdShape::KT;
-    constexpr int RS = FwdShape::rec_floats(D);
+template <int D, int OT, int BASIS, int NT>
+__global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
+    constexpr int Q = FwdShape::Q, TQ = NT * Q, KT = FwdShape::KT;
     constexpr int OP = OT / 2;            // packed output pairs
     constexpr int OTS = OT > 0 ? OT : 1;
+    constexpr int OPS = OP > 0 ? OP : 1;
 
     extern __shared__ __align__(16) float smem[];
-    float* stage = smem;                                  // [RC][KC][RS]
-    float* Ws = stage + (size_t)a.RC * a.KC * RS;         // [KC][OT]
-    float* gtab = Ws + (size_t)a.KC * (OT > 0 ? OT : 0);  // [RC][TQ]
+    const int KCT = a.KC / KT;                                  // kernel tiles per region in a stage
+    float4* stage4 = reinterpret_cast<float4*>(smem);           // [RC][KCT][D+1] float4
+    float* Ws = smem + (size_t)a.RC * KCT * (D + 1) * 4;        // [KC][OT]
+    float* gtab = Ws + (size_t)a.KC * (OT > 0 ? OT : 0);        // [RC][NT] float4
+    float* stage = smem;
 
     const int tid = threadIdx.x;
     const int R = a.R, K = a.K, RC = a.RC, KC = a.KC;
@@ -65,7 +70,7 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
         }
 
         // ---- output accumulators start at the bias ----
-        float2 y2[Q][OP > 0 ? OP : 1];
+        float2 y2[Q][OPS];
         if (OT > 0) {
 #pragma unroll
             for (int op = 0; op < OP; ++op) {
@@ -80,7 +85,7 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
         for (int rch = 0; rch < n_rch; ++rch) {
             const int r0 = rch * RC;
             const int rc = min(RC, R - r0);
-            float4* gcol = reinterpret_cast<float4*>(gtab) + tid;  // + rr * (TQ/4)
+            float4* gcol = reinterpret_cast<float4*>(gtab) + tid;  // + rr * NT
 
             // ---- gate table for this region chunk: thread-private columns, no barrier ----
             if (a.gate_ext != nullptr) {
@@ -90,13 +95,13 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
                     g.y = (q0 + 1 < a.B) ? __ldg(a.gate_ext + (q0 + 1) * R + r0 + rr) : 0.f;
                     g.z = (q0 + 2 < a.B) ? __ldg(a.gate_ext + (q0 + 2) * R + r0 + rr) : 0.f;
                     g.w = (q0 + 3 < a.B) ? __ldg(a.gate_ext + (q0 + 3) * R + r0 + rr) : 0.f;
-                    gcol[rr * (TQ / 4)] = g;
+                    gcol[rr * NT] = g;
                 }
             } else {
                 const int S = a.gd.S;
                 for (int rr = 0; rr < rc; ++rr) {
                     const float one = (r0 + rr < a.gd.num_ranges) ? 1.f : 0.f;
-                    gcol[rr * (TQ / 4)] = make_float4(one, one, one, one);
+                    gcol[rr * NT] = make_float4(one, one, one, one);
                 }
                 const int rlim = min(rc, a.gd.num_ranges - r0);
 #pragma unroll
@@ -113,9 +118,9 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
                             f.w = gate_sigmoid(k2, x2[1][j].y - lb) * gate_sigmoid(k2, ub - x2[1][j].y);
                             for (int rr = 0; rr < rlim; ++rr) {
                                 if (__ldg(a.gd.ranges + (r0 + rr) * S + j) == i - ob) {
-                                    float4 g = gcol[rr * (TQ / 4)];
+                                    float4 g = gcol[rr * NT];
                                     g.x *= f.x; g.y *= f.y; g.z *= f.z; g.w *= f.w;
-                                    gcol[rr * (TQ / 4)] = g;
+                                    gcol[rr * NT] = g;
                                 }
                             }
                         }
@@ -128,29 +133,22 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
                 const int kc = min(KC, K - k0);
                 const int kcp = ((kc + KT - 1) / KT) * KT;
 
-                // ---- stage parameters of (region chunk, kernel chunk) ----
+                // ---- stage parameters of (region chunk, kernel chunk), transposed per 4-kernel tile ----
                 if (!(a.stage_once && staged)) {
                     __syncthreads();  // everyone is done with the previous stage
                     for (int idx = tid; idx < rc * kcp; idx += NT) {
                         const int rr = idx / kcp, kk = idx - rr * kcp;
-                        float* rec = stage + ((size_t)rr * KC + kk) * RS;
+                        float* t = stage + ((size_t)rr * KCT + (kk >> 2)) * ((D + 1) * 4) + (kk & 3);
                         if (kk < kc) {
                             const size_t rk = (size_t)(r0 + rr) * K + (k0 + kk);
 #pragma unroll
-                            for (int j = 0; j < D; ++j) {
-                                const float c = j < a.Dsrc ? -__ldg(a.centers + rk * a.Dsrc + j) : 0.f;
-                                rec[2 * j] = c;
-                                rec[2 * j + 1] = c;
-                            }
-                            const float s = width_scale<BASIS>(__ldg(a.log_sigs + rk));
-                            rec[2 * D] = s;
-                            rec[2 * D + 1] = s;
+                            for (int j = 0; j < D; ++j)
+                                t[4 * j] = j < a.Dsrc ? -__ldg(a.centers + rk * a.Dsrc + j) : 0.f;
+                            t[4 * D] = width_scale<BASIS>(__ldg(a.log_sigs + rk));
                         } else {
 #pragma unroll
-                            for (int j = 0; j < 2 * D + 2; ++j) rec[j] = 0.f;
+                            for (int j = 0; j <= D; ++j) t[4 * j] = 0.f;
                         }
-#pragma unroll
-                        for (int j = 2 * D + 2; j < RS; ++j) rec[j] = 0.f;
                     }
                     if (OT > 0) {
                         for (int idx = tid; idx < kcp * OTS; idx += NT) {
@@ -163,54 +161,22 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
                     staged = true;
                 }
 
-                // ---- hot loop ----
-                for (int kt = 0; kt < kcp; kt += KT) {
-                    float2 h2[KT][2];
+                // ---- hot loop: (kernel tile, region) steps, blend pipelined by one step ----
+                float2 h2[KT][2], ph[KT][2], ea[KT][2];   // blend accumulators, basis values, basis arguments
+                float2 gp[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
 #pragma unroll
-                    for (int kk = 0; kk < KT; ++kk) h2[kk][0] = h2[kk][1] = make_float2(0.f, 0.f);
+                for (int kk = 0; kk < KT; ++kk) {
+                    h2[kk][0] = h2[kk][1] = make_float2(0.f, 0.f);
+                    ea[kk][0] = ea[kk][1] = make_float2(1.f, 1.f);   // finite basis value, blended with gate 0
+                }
 
-                    for (int rr = 0; rr < rc; ++rr) {
-                        const float4 g4 = gcol[rr * (TQ / 4)];
-                        const float2 g2[2] = {make_float2(g4.x, g4.y), make_float2(g4.z, g4.w)};
-                        const float4* rec4 =
-                            reinterpret_cast<const float4*>(stage + ((size_t)rr * KC + kt) * RS);
-#pragma unroll
-                        for (int kk = 0; kk < KT; ++kk) {
-                            float v[RS];
-#pragma unroll
-                            for (int i = 0; i < RS / 4; ++i) {
-                                const float4 t = rec4[kk * (RS / 4) + i];
-                                v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-                            }
-                            const float2 sc = make_float2(v[2 * D], v[2 * D + 1]);
-#pragma unroll
-                            for (int p = 0; p < 2; ++p) {
-                                float2 t = add2(x2[p][0], make_float2(v[0], v[1]));
-                                float2 acc = mul2(t, t);
-#pragma unroll
-                                for (int j = 1; j < D; ++j) {
-                                    t = add2(x2[p][j], make_float2(v[2 * j], v[2 * j + 1]));
-                                    acc = fma2(t, t, acc);
-                                }
-                                float2 phi;
-                                if (BASIS == IRBFN_BASIS_GAUSSIAN) {
-                                    const float2 e = mul2(acc, sc);
-                                    phi = make_float2(ex2_approx(e.x), ex2_approx(e.y));
-                                } else {
-                                    const float2 e = fma2(acc, sc, make_float2(1.f, 1.f));
-                                    phi = make_float2(rcp_approx(e.x), rcp_approx(e.y));
-                                }
-                                h2[kk][p] = fma2(g2[p], phi, h2[kk][p]);
-                            }
-                        }
-                    }
-
-                    // ---- readout of the finished kernel tile: y += h_k * W[k,:] ----
+                // y += h . W[kt .. kt+3, :] for the finished kernel tile at chunk offset kt
+                auto readout = [&](int kt) {
                     if (OT > 0) {
 #pragma unroll
                         for (int kk = 0; kk < KT; ++kk) {
                             const float2* w2 = reinterpret_cast<const float2*>(Ws + (size_t)(kt + kk) * OTS);
-                            float2 wv[OP > 0 ? OP : 1];
+                            float2 wv[OPS];
 #pragma unroll
                             for (int op = 0; op < OP; ++op) wv[op] = w2[op];
 #pragma unroll
@@ -224,27 +190,108 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
                             }
                         }
                     }
-                    if (a.hidden != nullptr) {
+                };
+                auto store_hidden = [&](int kt) {
 #pragma unroll
-                        for (int kk = 0; kk < KT; ++kk) {
-                            const int k = k0 + kt + kk;
-                            if (k < K) {
+                    for (int kk = 0; kk < KT; ++kk) {
+                        const int k = k0 + kt + kk;
+                        if (k < K) {
 #pragma unroll
-                                for (int p = 0; p < 2; ++p) {
-                                    const long long qa = q0 + 2 * p, qb = qa + 1;
-                                    if (qa < a.B) {
-                                        float* hp = a.hidden + qa * K + k;
-                                        *hp = (rch > 0 ? *hp : 0.f) + h2[kk][p].x;
-                                    }
-                                    if (qb < a.B) {
-                                        float* hp = a.hidden + qb * K + k;
-                                        *hp = (rch > 0 ? *hp : 0.f) + h2[kk][p].y;
-                                    }
+                            for (int p = 0; p < 2; ++p) {
+                                const long long qa = q0 + 2 * p, qb = qa + 1;
+                                if (qa < a.B) {
+                                    float* hp = a.hidden + qa * K + k;
+                                    *hp = (rch > 0 ? *hp : 0.f) + h2[kk][p].x;
+                                }
+                                if (qb < a.B) {
+                                    float* hp = a.hidden + qb * K + k;
+                                    *hp = (rch > 0 ? *hp : 0.f) + h2[kk][p].y;
                                 }
                             }
                         }
                     }
+                };
+                // basis function of the PREVIOUS step's arguments: MUFU number i of 16 (4 kernels x 4 queries)
+                auto mufu = [&](int i) {
+                    const int kk = i >> 2, p = (i >> 1) & 1;
+                    float& src = (i & 1) ? ea[kk][p].y : ea[kk][p].x;
+                    float& dst = (i & 1) ? ph[kk][p].y : ph[kk][p].x;
+                    dst = BASIS == IRBFN_BASIS_GAUSSIAN ? ex2_approx(src) : rcp_approx(src);
+                };
+                // distances of one step: feature-outer, 8 independent packed chains; the 16 MUFUs of the
+                // previous step are spread between the features so that the XU never sees a burst and the
+                // issue gaps a MUFU leaves are filled with this step's packed arithmetic.
+                auto distances = [&](const float4* rec, float2 (&acc)[KT][2]) {
+#pragma unroll
+                    for (int j = 0; j < D; ++j) {
+                        const float4 c4 = rec[j];
+                        const float c[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+                        for (int kk = 0; kk < KT; ++kk) {
+#pragma unroll
+                            for (int p = 0; p < 2; ++p) {
+                                const float2 d = add2(x2[p][j], dup2(c[kk]));
+                                acc[kk][p] = j == 0 ? mul2(d, d) : fma2(d, d, acc[kk][p]);
+                            }
+                        }
+#pragma unroll
+                        for (int i = (16 * j) / D; i < (16 * (j + 1)) / D; ++i) mufu(i);
+                    }
+                };
+                // blend of the PREVIOUS step
+                auto blend = [&]() {
+#pragma unroll
+                    for (int kk = 0; kk < KT; ++kk) {
+                        h2[kk][0] = fma2(gp[0], ph[kk][0], h2[kk][0]);
+                        h2[kk][1] = fma2(gp[1], ph[kk][1], h2[kk][1]);
+                    }
+                };
+                // arguments of this step's basis function; evaluated during the next step's distances
+                auto scale = [&](const float4* rec, const float2 (&acc)[KT][2], const float4 g4) {
+                    const float4 s4 = rec[D];
+                    const float sc[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+                    for (int kk = 0; kk < KT; ++kk) {
+#pragma unroll
+                        for (int p = 0; p < 2; ++p) {
+                            if (BASIS == IRBFN_BASIS_GAUSSIAN) ea[kk][p] = mul2(acc[kk][p], dup2(sc[kk]));
+                            else ea[kk][p] = fma2(acc[kk][p], dup2(sc[kk]), make_float2(1.f, 1.f));
+                        }
+                    }
+                    gp[0] = make_float2(g4.x, g4.y);
+                    gp[1] = make_float2(g4.z, g4.w);
+                };
+
+                const size_t rstride = (size_t)KCT * (D + 1);
+                for (int kt = 0; kt < kcp; kt += KT) {
+                    const float4* rec = stage4 + (size_t)(kt >> 2) * (D + 1);
+                    {   // first region of the tile (peeled): also closes the previous kernel tile.
+                        // At kt == 0 the pipeline is empty (h and gp are zero): blend and readout add 0.
+                        const float4 g4 = gcol[0];
+                        float2 acc[KT][2];
+                        distances(rec, acc);
+                        blend();
+                        readout(kt > 0 ? kt - KT : 0);
+                        scale(rec, acc, g4);
+                        if (a.hidden != nullptr && kt > 0) store_hidden(kt - KT);
+#pragma unroll
+                        for (int kk = 0; kk < KT; ++kk) h2[kk][0] = h2[kk][1] = make_float2(0.f, 0.f);
+                    }
+                    for (int rr = 1; rr < rc; ++rr) {   // branch-free steady state
+                        rec += rstride;
+                        const float4 g4 = gcol[rr * NT];
+                        float2 acc[KT][2];
+                        distances(rec, acc);
+                        blend();
+                        scale(rec, acc, g4);
+                    }
                 }
+                // drain the pipeline: basis + blend of the last step, close the last kernel tile
+#pragma unroll
+                for (int i = 0; i < 16; ++i) mufu(i);
+                blend();
+                readout(kcp - KT);
+                if (a.hidden != nullptr) store_hidden(kcp - KT);
             }
         }
 
@@ -266,33 +313,34 @@ __global__ void __launch_bounds__(FwdShape::NT, 1) irbfn_fwd_kernel(const FwdArg
     }
 }
 
-// Host-side: pick the instantiation for (OT, basis) and launch.  Returns a cudaError_t as int.
-template <int D, int OT>
-inline int launch_fwd_ot(const FwdArgs& a, int basis, int grid, size_t smem, cudaStream_t st) {
-    cudaError_t e;
-    if (basis == IRBFN_BASIS_GAUSSIAN) {
-        auto kern = irbfn_fwd_kernel<D, OT, IRBFN_BASIS_GAUSSIAN>;
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        kern<<<grid, FwdShape::NT, smem, st>>>(a);
-    } else {
-        auto kern = irbfn_fwd_kernel<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC>;
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        kern<<<grid, FwdShape::NT, smem, st>>>(a);
-    }
+// Host-side: pick the instantiation for (OT, basis, threads) and launch.  Returns a cudaError_t as int.
+template <int D, int OT, int BASIS, int NT>
+inline int launch_fwd_inst(const FwdArgs& a, int grid, size_t smem, cudaStream_t st) {
+    auto kern = irbfn_fwd_kernel<D, OT, BASIS, NT>;
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<grid, NT, smem, st>>>(a);
     return (int)cudaGetLastError();
 }
 
+template <int D, int OT>
+inline int launch_fwd_ot(const FwdArgs& a, int basis, int nt, int grid, size_t smem, cudaStream_t st) {
+    if (basis == IRBFN_BASIS_GAUSSIAN)
+        return nt == 512 ? launch_fwd_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 512>(a, grid, smem, st)
+                         : launch_fwd_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 256>(a, grid, smem, st);
+    return nt == 512 ? launch_fwd_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 512>(a, grid, smem, st)
+                     : launch_fwd_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 256>(a, grid, smem, st);
+}
+
 template <int D>
-inline int launch_fwd(const FwdArgs& a, int OT, int basis, int grid, size_t smem, cudaStream_t st) {
+inline int launch_fwd(const FwdArgs& a, int OT, int basis, int nt, int grid, size_t smem, cudaStream_t st) {
     switch (OT) {
-        case 0: return launch_fwd_ot<D, 0>(a, basis, grid, smem, st);
-        case 2: return launch_fwd_ot<D, 2>(a, basis, grid, smem, st);
-        case 4: return launch_fwd_ot<D, 4>(a, basis, grid, smem, st);
-        case 8: return launch_fwd_ot<D, 8>(a, basis, grid, smem, st);
-        case 10: return launch_fwd_ot<D, 10>(a, basis, grid, smem, st);
-        case 16: return launch_fwd_ot<D, 16>(a, basis, grid, smem, st);
+        case 0: return launch_fwd_ot<D, 0>(a, basis, nt, grid, smem, st);
+        case 2: return launch_fwd_ot<D, 2>(a, basis, nt, grid, smem, st);
+        case 4: return launch_fwd_ot<D, 4>(a, basis, nt, grid, smem, st);
+        case 8: return launch_fwd_ot<D, 8>(a, basis, nt, grid, smem, st);
+        case 10: return launch_fwd_ot<D, 10>(a, basis, nt, grid, smem, st);
+        case 16: return launch_fwd_ot<D, 16>(a, basis, nt, grid, smem, st);
         default: return (int)cudaErrorInvalidValue;
     }
 }

@@ -10,8 +10,8 @@
 #define IRBFN_CAT(a, b) IRBFN_CAT_(a, b)
 
 namespace irbfn {
-int IRBFN_CAT(launch_fwd_d, IRBFN_D)(const FwdArgs& a, int OT, int basis, int grid, size_t smem,
-                                     cudaStream_t st) {
-    return launch_fwd<IRBFN_D>(a, OT, basis, grid, smem, st);
+int IRBFN_CAT(launch_fwd_d, IRBFN_D)(const FwdArgs& a, int OT, int basis, int nt, int grid,
+                                     size_t smem, cudaStream_t st) {
+    return launch_fwd<IRBFN_D>(a, OT, basis, nt, grid, smem, st);
 }
 }  // namespace irbfn

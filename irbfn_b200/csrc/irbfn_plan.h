@@ -6,10 +6,16 @@
 namespace irbfn {
 
 // Forward tile geometry; must match FwdShape in irbfn_fwd.cuh.
-constexpr int kFwdTQ = 1024;  // queries per CTA tile
-constexpr int kFwdKT = 4;     // kernels per register tile
+constexpr int kFwdQ = 4;      // queries per thread
+constexpr int kFwdKT = 4;     // kernels per register tile and per transposed shared-memory tile
+constexpr int kFwdTQ = 1024;  // queries per CTA tile of the 256-thread kernels (backward X)
 
-inline int fwd_rec_floats(int D) { return ((2 * D + 2 + 3) / 4) * 4; }
+// floats of one transposed 4-kernel tile: rows -c_0..-c_{D-1} and the width scales
+inline int fwd_tile_floats(int D) { return (D + 1) * 4; }
+
+// Threads per CTA of the forward kernel: 512 (<= 128 registers per thread) while the output
+// accumulators are small, 256 for the wide output windows.
+inline int fwd_threads_for(int OT) { (void)OT; return 256; }
 
 // Compiled output-window widths of the forward kernel.
 inline int fwd_ot_for(int ocur) {
@@ -26,31 +32,35 @@ struct FwdPlan {
     int KC;          // kernels per stage (multiple of kFwdKT)
     int stage_once;  // whole parameter set resident: staged once per CTA
     size_t smem_bytes;
+    int NT;          // threads per CTA (forward only)
 };
 
-inline size_t fwd_smem_bytes(int RC, int KC, int D, int OT) {
-    return ((size_t)RC * KC * fwd_rec_floats(D) + (size_t)KC * OT + (size_t)RC * kFwdTQ) * sizeof(float);
+// stage [RC][KC/4] tiles + readout rows [KC][OT] + gate table [RC][NT] float4
+inline size_t fwd_smem_bytes(int RC, int KC, int D, int OT, int NT) {
+    return ((size_t)RC * (KC / kFwdKT) * fwd_tile_floats(D) + (size_t)KC * OT + (size_t)RC * NT * kFwdQ) *
+           sizeof(float);
 }
 
 inline bool plan_forward(int R, int K, int D, int OT, int smem_limit, FwdPlan* p) {
+    const int NT = fwd_threads_for(OT);
     const int Kp = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
-    if (fwd_smem_bytes(R, Kp, D, OT) <= (size_t)smem_limit) {
-        *p = FwdPlan{R, Kp, 1, fwd_smem_bytes(R, Kp, D, OT)};
+    if (fwd_smem_bytes(R, Kp, D, OT, NT) <= (size_t)smem_limit) {
+        *p = FwdPlan{R, Kp, 1, fwd_smem_bytes(R, Kp, D, OT, NT), NT};
         return true;
     }
     const int want = Kp < 64 ? Kp : 64;
-    const int cands[5] = {R < 16 ? R : 16, 8, 4, 2, 1};
-    for (int i = 0; i < 5; ++i) {
+    const int cands[6] = {R < 32 ? R : 32, 16, 8, 4, 2, 1};
+    for (int i = 0; i < 6; ++i) {
         const int RC = cands[i] < R ? cands[i] : R;
         if (RC <= 0) continue;
-        const size_t fixed = (size_t)RC * kFwdTQ * sizeof(float);
+        const size_t fixed = (size_t)RC * NT * kFwdQ * sizeof(float);
         if (fixed >= (size_t)smem_limit) continue;
-        const size_t per_k = ((size_t)RC * fwd_rec_floats(D) + OT) * sizeof(float);
+        const size_t per_k = ((size_t)RC * fwd_tile_floats(D) / kFwdKT + OT) * sizeof(float);
         long long KC = (long long)(((size_t)smem_limit - fixed) / per_k);
         KC = (KC / kFwdKT) * kFwdKT;
         if (KC > Kp) KC = Kp;
         if (KC >= want || (RC == 1 && KC >= kFwdKT)) {
-            *p = FwdPlan{RC, (int)KC, 0, fwd_smem_bytes(RC, (int)KC, D, OT)};
+            *p = FwdPlan{RC, (int)KC, 0, fwd_smem_bytes(RC, (int)KC, D, OT, NT), NT};
             return true;
         }
     }
