@@ -150,6 +150,15 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
                    unsigned grad_mask, void* workspace, size_t workspace_bytes,
                    irbfn_stream_t stream);
 
+/*
+ * Introspection (host only, no device needed): how irbfn_forward cuts the (R,K) parameter set into
+ * shared-memory stages for a device with smem_limit_bytes of opt-in shared memory per block
+ * (B200: 232448).  regions_per_stage == R and kernels_per_stage >= K means the whole parameter set
+ * is staged once per CTA.  Returns IRBFN_ERR_BAD_DIMS if no plan exists.
+ */
+int irbfn_forward_plan(int R, int K, int D, int O, int smem_limit_bytes, int* regions_per_stage,
+                       int* kernels_per_stage, int* threads_per_block, size_t* smem_bytes);
+
 /* gamma (B,R) of the tanh region gate alone (model.py:42-95). */
 int irbfn_region_gate(const float* x, const IrbfnGateDesc* gd, float* gamma, int64_t B, int R,
                       int D, irbfn_stream_t stream);

@@ -29,7 +29,7 @@ ABI_VERSION = 1
 EXPORTED_SYMBOLS = (
     "irbfn_abi_version", "irbfn_error_string", "irbfn_last_error_detail", "irbfn_forward_workspace_bytes", "irbfn_forward",
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
-    "irbfn_softmax_gate", "irbfn_fp32_microbench", "irbfn_pipe_microbench",
+    "irbfn_softmax_gate", "irbfn_fp32_microbench", "irbfn_pipe_microbench", "irbfn_forward_plan",
 )
 
 
@@ -85,6 +85,8 @@ def load():
     lib.irbfn_fp32_microbench.restype = i
     lib.irbfn_fp32_microbench.argtypes = [i, i, i, p, C.POINTER(C.c_double),
                                           C.POINTER(C.c_double), C.POINTER(C.c_float), p]
+    lib.irbfn_forward_plan.restype = i
+    lib.irbfn_forward_plan.argtypes = [i, i, i, i, i, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(sz)]
     lib.irbfn_pipe_microbench.restype = i
     lib.irbfn_pipe_microbench.argtypes = [i, i, i, p, C.POINTER(C.c_double), C.POINTER(C.c_float), p]
     if lib.irbfn_abi_version() != ABI_VERSION:

@@ -255,6 +255,20 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
     return IRBFN_OK;
 }
 
+int irbfn_forward_plan(int R, int K, int D, int O, int smem_limit_bytes, int* regions_per_stage,
+                       int* kernels_per_stage, int* threads_per_block, size_t* smem_bytes) {
+    if (R <= 0 || K <= 0 || D <= 0 || O < 0 || smem_limit_bytes <= 0) return IRBFN_ERR_BAD_DIMS;
+    if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
+    FwdPlan plan;
+    if (!plan_forward(R, K, D < 4 ? 4 : D, fwd_ot_for(O > 16 ? 16 : O), smem_limit_bytes, &plan))
+        return IRBFN_ERR_BAD_DIMS;
+    if (regions_per_stage) *regions_per_stage = plan.RC;
+    if (kernels_per_stage) *kernels_per_stage = plan.KC;
+    if (threads_per_block) *threads_per_block = plan.NT;
+    if (smem_bytes) *smem_bytes = plan.smem_bytes;
+    return IRBFN_OK;
+}
+
 int irbfn_region_gate(const float* x, const IrbfnGateDesc* gd, float* gamma, int64_t B, int R,
                       int D, irbfn_stream_t stream) {
     if (B < 0 || R <= 0 || D <= 0) return IRBFN_ERR_BAD_DIMS;
