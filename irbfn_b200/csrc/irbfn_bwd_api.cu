@@ -8,11 +8,11 @@
 #include "irbfn_plan.h"
 
 namespace irbfn {
-int launch_bwd_p_d4(const BwdPArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_bwd_p_d5(const BwdPArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_bwd_p_d6(const BwdPArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_bwd_p_d7(const BwdPArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_bwd_p_d8(const BwdPArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_p_d4(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_p_d5(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_p_d6(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_p_d7(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_p_d8(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_x_d4(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
 int launch_bwd_x_d5(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
 int launch_bwd_x_d6(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
@@ -44,39 +44,53 @@ struct ReduceArgs {
     int splits, db_blocks, R, K, D, Dsrc, PW, O, o0, ocur;
 };
 
+// One warp per output element: lane l sums terms l, l+32, ... in order, then a fixed xor-shuffle
+// tree combines the 32 lane sums.  The order depends only on the launch geometry: deterministic.
+__device__ __forceinline__ double warp_sum_fixed(double s) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    return s;
+}
+
 __global__ void __launch_bounds__(256) reduce_p_kernel(const ReduceArgs a) {
     const long long RK = (long long)a.R * a.K;
     const long long nC = a.dC ? RK * a.Dsrc : 0;
     const long long nL = a.dLS ? RK : 0;
     const long long nW = a.dW ? (long long)a.K * a.ocur : 0;
     const long long nB = a.db ? a.O : 0;
-    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const long long e = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;   // warp-uniform
     const size_t sstride = (size_t)RK * a.PW;
     if (e < nC) {
         const long long f = e / a.Dsrc;
         const int j = (int)(e - f * a.Dsrc);
         double s = 0.0;
-        for (int sp = 0; sp < a.splits; ++sp) s += (double)a.part[sp * sstride + (size_t)f * a.PW + j];
-        a.dC[e] = (float)(2.0 * exp(-2.0 * (double)a.log_sigs[f]) * s);
+        for (int sp = lane; sp < a.splits; sp += 32) s += (double)a.part[sp * sstride + (size_t)f * a.PW + j];
+        s = warp_sum_fixed(s);
+        if (lane == 0) a.dC[e] = (float)(2.0 * exp(-2.0 * (double)a.log_sigs[f]) * s);
     } else if (e < nC + nL) {
         const long long f = e - nC;
         double s = 0.0;
-        for (int sp = 0; sp < a.splits; ++sp) s += (double)a.part[sp * sstride + (size_t)f * a.PW + a.D];
-        a.dLS[f] = (float)(2.0 * exp(-2.0 * (double)a.log_sigs[f]) * s);
+        for (int sp = lane; sp < a.splits; sp += 32) s += (double)a.part[sp * sstride + (size_t)f * a.PW + a.D];
+        s = warp_sum_fixed(s);
+        if (lane == 0) a.dLS[f] = (float)(2.0 * exp(-2.0 * (double)a.log_sigs[f]) * s);
     } else if (e < nC + nL + nW) {
         const long long i = e - nC - nL;
         const int k = (int)(i / a.ocur), o = (int)(i - (long long)k * a.ocur);
         double s = 0.0;
-        for (int r = 0; r < a.R; ++r) {
-            const size_t f = (size_t)r * a.K + k;
-            for (int sp = 0; sp < a.splits; ++sp) s += (double)a.part[sp * sstride + f * a.PW + a.D + 1 + o];
+        const long long terms = (long long)a.R * a.splits;
+        for (long long t = lane; t < terms; t += 32) {
+            const int r = (int)(t / a.splits), sp = (int)(t - (long long)r * a.splits);
+            s += (double)a.part[sp * sstride + ((size_t)r * a.K + k) * a.PW + a.D + 1 + o];
         }
-        a.dW[(size_t)k * a.O + a.o0 + o] = (float)s;
+        s = warp_sum_fixed(s);
+        if (lane == 0) a.dW[(size_t)k * a.O + a.o0 + o] = (float)s;
     } else if (e < nC + nL + nW + nB) {
         const int o = (int)(e - nC - nL - nW);
         double s = 0.0;
-        for (int sp = 0; sp < a.db_blocks; ++sp) s += (double)a.part_db[(size_t)sp * a.O + o];
-        a.db[o] = (float)s;
+        for (int sp = lane; sp < a.db_blocks; sp += 32) s += (double)a.part_db[(size_t)sp * a.O + o];
+        s = warp_sum_fixed(s);
+        if (lane == 0) a.db[o] = (float)s;
     }
 }
 
@@ -333,11 +347,11 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             const int grid = pp.nchunks * pp.splits;
             int e;
             switch (DT) {
-                case 4: e = launch_bwd_p_d4(a, OT, basis, grid, pp.NT, pp.smem_bytes, st); break;
-                case 5: e = launch_bwd_p_d5(a, OT, basis, grid, pp.NT, pp.smem_bytes, st); break;
-                case 6: e = launch_bwd_p_d6(a, OT, basis, grid, pp.NT, pp.smem_bytes, st); break;
-                case 7: e = launch_bwd_p_d7(a, OT, basis, grid, pp.NT, pp.smem_bytes, st); break;
-                default: e = launch_bwd_p_d8(a, OT, basis, grid, pp.NT, pp.smem_bytes, st); break;
+                case 4: e = launch_bwd_p_d4(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                case 5: e = launch_bwd_p_d5(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                case 6: e = launch_bwd_p_d6(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                case 7: e = launch_bwd_p_d7(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                default: e = launch_bwd_p_d8(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
             }
             if (e != 0) return note_cuda_error("irbfn_bwd_p_kernel", e);
             ReduceArgs r{};
@@ -355,7 +369,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
                 { const cudaError_t ce = cudaGetLastError(); if (ce != cudaSuccess) return note_cuda_error("db_partial_kernel", (int)ce); }
             }
             if (n > 0) {
-                reduce_p_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(r);
+                reduce_p_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(r);   // one warp per element
                 { const cudaError_t ce = cudaGetLastError(); if (ce != cudaSuccess) return note_cuda_error("reduce_p_kernel", (int)ce); }
             }
             o0 += ocur;

@@ -4,15 +4,18 @@
 //   scripts/train_nmpc.py:297,416 ; scripts/train_nmpc_frenet.py:388,416,448
 //   forward being differentiated: model.py:187-196, flax_rbf.py:275-283
 //
-// Design ("backward kernel P"): the roles of the forward are swapped.
+// Design: the roles of the forward are swapped.
 //   * parameter-stationary: a thread owns NKP packed PAIRS of kernels (f, f+1) of the flat
-//     (region,kernel) index; their centres, width scales and all of their gradient accumulators
-//     (D + 1 + OT packed floats per pair) live in registers for the whole launch, so the
-//     cross-query reduction of dC / dlog_sig / dW costs nothing per query: no shuffles, no atomics.
-//   * queries stream through shared memory in tiles of TQ: x duplicated as (x_j, x_j) so a
-//     broadcast LDS.128 yields two ready packed operands; dy duplicated the same way; the gate
-//     slab gamma[q, r_lo..r_hi] and dh[q,k] = dy[q,:] W[k,:]^T (+ dhidden) are computed once per
-//     tile.  The next tile's raw rows arrive by cp.async while the current one is consumed.
+//     (region,kernel) index; their centres, width scales, readout rows and all of their gradient
+//     accumulators (D + 1 + OT packed floats per pair) live in registers for the whole launch, so
+//     the cross-query reduction of dC / dlog_sig / dW costs nothing per query: no shuffles, no atomics.
+//   * queries stream through shared memory in tiles of TQ rows [x | dy | gamma slab], written
+//     straight into their compute layout by cp.async (double buffered, one barrier per tile).  A
+//     query's scalars are broadcast operands of the packed instructions (SASS `Rn.F32`), so nothing
+//     is duplicated in shared memory.
+//   * dh_k = dy . W[k,:] is formed in the thread from its own readout rows when the output window
+//     is narrow (DHT = 1: O <= 4, the NMPC shapes); otherwise (wide O, or a dhidden cotangent) a
+//     per-tile table dh[q][k] is built once per tile and shared by all regions.
 //   * phi is recomputed from x and the parameters (nothing saved by the forward).
 //   * grid = splits x chunks: a chunk is a contiguous range of kernel pairs, a split a strided
 //     set of query tiles.  Every CTA writes its raw partial sums to the workspace once; a second
@@ -50,39 +53,45 @@ __device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-template <int D, int OT, int BASIS, int NKP>
-__global__ void __launch_bounds__(256, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
-    constexpr int OP = OT / 2;                  // dy columns come duplicated: (dy_o, dy_o)
+// shared-memory row strides (floats); must match bwdp_smem_floats in irbfn_plan.h
+__host__ __device__ constexpr int bwdp_xs(int D) { return ((D + 3) / 4) * 4; }
+__host__ __device__ inline int bwdp_ds(int O) { return O <= 0 ? 0 : (O <= 2 ? 2 : ((O + 3) / 4) * 4); }
+
+template <int D, int OT, int BASIS, int NKP, int DHT>
+__global__ void __launch_bounds__(320, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
     constexpr int OTS = OT > 0 ? OT : 1;
     constexpr int PW = D + 1 + OT;
-    constexpr int XS = ((2 * D + 3) / 4) * 4;   // row stride of xs: keeps LDS.128 aligned for odd D
+    constexpr int XS = bwdp_xs(D);
     const int NT = blockDim.x;
     const int tid = threadIdx.x;
     const int chunk = blockIdx.x % a.nchunks;
     const int split = blockIdx.x / a.nchunks;
     const int RK = a.R * a.K;
     const int TQ = a.TQ, O = a.O, Dsrc = a.Dsrc, Kspan = a.Kspan, Rspan = a.Rspan, K = a.K;
-    const int GS = Rspan + 1;                   // gate table row stride (last column is zero)
+    const int GS = Rspan + 1;                   // gate row stride (last column stays zero)
+    const int DS = bwdp_ds(O);                  // dy row stride (pad columns stay zero)
 
     const int f_lo = 2 * chunk * a.pairs_per_chunk;
     const int f_len = 2 * a.pairs_per_chunk;
     const int f_hi = min(f_lo + f_len, RK);     // exclusive
     const int r_lo = f_lo / K;
     const bool k_direct = f_len >= K;           // dh table indexed by k itself (else by f - f_lo)
-    const int raw_dh = a.dhidden != nullptr ? Kspan : 0;
+    const bool has_dhid = a.dhidden != nullptr;
 
     extern __shared__ __align__(16) float smem[];
-    const int raw_stride = TQ * (Dsrc + O + Rspan + raw_dh);
-    float* raw0 = smem;                                   // 2 raw stages
-    float* xs = smem + 2 * (size_t)raw_stride;            // [TQ][XS]  (x_j, x_j) pairs
-    xs += ((4 - ((xs - smem) & 3)) & 3);
-    float* dys = xs + (size_t)TQ * XS;                    // [TQ][2*OT]
-    float* dhs = dys + (size_t)TQ * 2 * OTS;              // [TQ][Kspan]
-    float* gs = dhs + (size_t)TQ * Kspan;                 // [TQ][GS]
+    // two stages of [xs | dys | gs | raw dhidden], then the dh table (DHT == 0 only)
+    const int st_x = 0, st_dy = st_x + TQ * XS, st_g = st_dy + TQ * DS;
+    const int st_dh = ((st_g + TQ * GS + 3) / 4) * 4;
+    const int stage_floats = ((st_dh + (has_dhid ? TQ * Kspan : 0) + 3) / 4) * 4;
+    float* dhs = smem + 2 * (size_t)stage_floats;  // [TQ][Kspan]
+
+    // zero both stages once: cp.async never writes the pad columns, they must read as 0
+    for (int i = tid; i < 2 * stage_floats; i += NT) smem[i] = 0.f;
 
     // ---- this thread's kernel pairs: parameters -> registers ----
     float2 nc2[NKP][D];   // (-c_j[f0], -c_j[f1])
     float2 sc2[NKP];      // width scale of (f0, f1)
+    float2 w2[NKP][DHT ? OTS : 1];  // readout rows (W[k0,o], W[k1,o])
     int kidx[NKP][2], ridx[NKP][2];
     bool contig[NKP];
 #pragma unroll
@@ -97,55 +106,130 @@ __global__ void __launch_bounds__(256, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
             const int r = fc / K, k = fc - r * K;
             kidx[p][h] = k_direct ? k : (fc - f_lo);
             ridx[p][h] = valid ? (r - r_lo) : Rspan;  // zero column for padding kernels
-            float s = valid ? width_scale<BASIS>(__ldg(a.log_sigs + fc)) : 0.f;
+            const float s = valid ? width_scale<BASIS>(__ldg(a.log_sigs + fc)) : 0.f;
             if (h == 0) sc2[p].x = s; else sc2[p].y = s;
 #pragma unroll
             for (int j = 0; j < D; ++j) {
                 const float c = (valid && j < Dsrc) ? -__ldg(a.centers + (size_t)fc * Dsrc + j) : 0.f;
                 if (h == 0) nc2[p][j].x = c; else nc2[p][j].y = c;
             }
+            if (DHT) {
+#pragma unroll
+                for (int o = 0; o < OT; ++o) {
+                    const float w = (valid && o < O) ? __ldg(a.W + (size_t)k * O + o) : 0.f;
+                    if (h == 0) w2[p][o].x = w; else w2[p][o].y = w;
+                }
+            }
         }
         contig[p] = (kidx[p][1] == kidx[p][0] + 1) && ((kidx[p][0] & 1) == 0);
     }
 
-    float2 aC[NKP][D], aL[NKP], aW[NKP][OP > 0 ? OP * 2 : 1];
+    float2 aC[NKP][D], aL[NKP], aW[NKP][OTS];
 #pragma unroll
     for (int p = 0; p < NKP; ++p) {
         aL[p] = make_float2(0.f, 0.f);
 #pragma unroll
         for (int j = 0; j < D; ++j) aC[p][j] = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int o = 0; o < OT; ++o) aW[p][o] = make_float2(0.f, 0.f);
+        for (int o = 0; o < OTS; ++o) aW[p][o] = make_float2(0.f, 0.f);
     }
 
     const long long ntiles = (a.B + TQ - 1) / TQ;
 
     auto issue_tile = [&](long long tile, int stage) {
-        float* raw = raw0 + (size_t)stage * raw_stride;
+        float* sb = smem + (size_t)stage * stage_floats;
         const long long q0 = tile * TQ;
         const int tq = (int)min((long long)TQ, a.B - q0);
-        float* rx = raw;
-        float* rdy = rx + (size_t)TQ * Dsrc;
-        float* rg = rdy + (size_t)TQ * O;
-        float* rdh = rg + (size_t)TQ * Rspan;
-        for (int i = tid; i < tq * Dsrc; i += NT) cp_async4(rx + i, a.x + q0 * Dsrc + i);
+        for (int i = tid; i < tq * Dsrc; i += NT) {
+            const int q = i / Dsrc, j = i - q * Dsrc;
+            cp_async4(sb + st_x + q * XS + j, a.x + q0 * Dsrc + i);
+        }
         if (a.dy != nullptr)
-            for (int i = tid; i < tq * O; i += NT) cp_async4(rdy + i, a.dy + q0 * O + i);
+            for (int i = tid; i < tq * O; i += NT) {
+                const int q = i / O, o = i - q * O;
+                cp_async4(sb + st_dy + q * DS + o, a.dy + q0 * O + i);
+            }
         for (int i = tid; i < tq * Rspan; i += NT) {
             const int q = i / Rspan, rr = i - q * Rspan;
             const int r = min(r_lo + rr, a.R - 1);
-            cp_async4(rg + i, a.gate + (q0 + q) * a.R + r);
+            cp_async4(sb + st_g + q * GS + rr, a.gate + (q0 + q) * a.R + r);
         }
-        if (raw_dh)
+        if (has_dhid)
             for (int i = tid; i < tq * Kspan; i += NT) {
                 const int q = i / Kspan, kk = i - q * Kspan;
                 int k = k_direct ? kk : (f_lo + kk) % K;
                 k = min(k, K - 1);
-                cp_async4(rdh + i, a.dhidden + (q0 + q) * K + k);
+                cp_async4(sb + st_dh + i, a.dhidden + (q0 + q) * K + k);
             }
         cp_async_commit();
     };
 
+    // one query of the current stage against all of this thread's kernel pairs
+    auto eval = [&](const float* sb, int q) {
+        float xv[XS];
+        {
+            const float4* xp = reinterpret_cast<const float4*>(sb + st_x + (size_t)q * XS);
+#pragma unroll
+            for (int i = 0; i < XS / 4; ++i) {
+                const float4 t = xp[i];
+                xv[4 * i] = t.x; xv[4 * i + 1] = t.y; xv[4 * i + 2] = t.z; xv[4 * i + 3] = t.w;
+            }
+        }
+        float dyv[OTS];
+        if (OT > 0) {
+            const float* dp = sb + st_dy + (size_t)q * DS;
+            if (DHT) {
+                const float2* d2p = reinterpret_cast<const float2*>(dp);
+#pragma unroll
+                for (int o = 0; o < OT / 2; ++o) { const float2 t = d2p[o]; dyv[2 * o] = t.x; dyv[2 * o + 1] = t.y; }
+            } else {
+#pragma unroll
+                for (int o = 0; o < OT; ++o) dyv[o] = o < a.ocur ? dp[a.o0 + o] : 0.f;
+            }
+        }
+        const float* gq = sb + st_g + (size_t)q * GS;
+        const float* dq = dhs + (size_t)q * Kspan;
+#pragma unroll
+        for (int p = 0; p < NKP; ++p) {
+            const float2 g2 = make_float2(gq[ridx[p][0]], gq[ridx[p][1]]);
+            float2 dh2;
+            if (DHT) {
+                dh2 = mul2(w2[p][0], dup2(dyv[0]));
+#pragma unroll
+                for (int o = 1; o < OT; ++o) dh2 = fma2(w2[p][o], dup2(dyv[o]), dh2);
+            } else if (contig[p]) {
+                dh2 = *reinterpret_cast<const float2*>(dq + kidx[p][0]);
+            } else {
+                dh2 = make_float2(dq[kidx[p][0]], dq[kidx[p][1]]);
+            }
+            float2 df[D];
+            df[0] = add2(nc2[p][0], dup2(xv[0]));
+            float2 d2 = mul2(df[0], df[0]);
+#pragma unroll
+            for (int j = 1; j < D; ++j) {
+                df[j] = add2(nc2[p][j], dup2(xv[j]));
+                d2 = fma2(df[j], df[j], d2);
+            }
+            float2 phi;
+            if (BASIS == IRBFN_BASIS_GAUSSIAN) {
+                const float2 e = mul2(d2, sc2[p]);
+                phi = make_float2(ex2_approx(e.x), ex2_approx(e.y));
+            } else {
+                const float2 e = fma2(d2, sc2[p], make_float2(1.f, 1.f));
+                phi = make_float2(rcp_approx(e.x), rcp_approx(e.y));
+            }
+            const float2 v = mul2(g2, phi);  // gamma * phi
+#pragma unroll
+            for (int o = 0; o < OT; ++o) aW[p][o] = fma2(v, dup2(dyv[o]), aW[p][o]);
+            float2 t = mul2(v, dh2);         // dh * gamma * phi   (= -dL/d(alpha^2), gaussian)
+            if (BASIS == IRBFN_BASIS_INVERSE_QUADRATIC) t = mul2(t, phi);
+#pragma unroll
+            for (int j = 0; j < D; ++j) aC[p][j] = fma2(t, df[j], aC[p][j]);
+            aL[p] = fma2(t, d2, aL[p]);
+        }
+    };
+
+    __syncthreads();  // zero fill is visible before any cp.async lands on it
     long long tile = split;
     int stage = 0;
     if (tile < ntiles) issue_tile(tile, 0);
@@ -153,96 +237,34 @@ __global__ void __launch_bounds__(256, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
     for (; tile < ntiles; tile += a.splits, stage ^= 1) {
         const long long q0 = tile * TQ;
         const int tq = (int)min((long long)TQ, a.B - q0);
+        const float* sb = smem + (size_t)stage * stage_floats;
         cp_async_wait_all();
-        __syncthreads();  // raw[stage] landed; everyone is done computing on the previous tile
-
-        // ---- transform raw rows into the compute layout ----
-        {
-            const float* raw = raw0 + (size_t)stage * raw_stride;
-            const float* rx = raw;
-            const float* rdy = rx + (size_t)TQ * Dsrc;
-            const float* rg = rdy + (size_t)TQ * O;
-            const float* rdh = rg + (size_t)TQ * Rspan;
-            for (int i = tid; i < tq * D; i += NT) {
-                const int q = i / D, j = i - q * D;
-                const float v = j < Dsrc ? rx[q * Dsrc + j] : 0.f;
-                *reinterpret_cast<float2*>(xs + (size_t)q * XS + 2 * j) = make_float2(v, v);
-            }
-            if (OT > 0)
-                for (int i = tid; i < tq * OT; i += NT) {
-                    const int q = i / OT, o = i - q * OT;
-                    const float v = o < a.ocur ? rdy[q * O + a.o0 + o] : 0.f;
-                    reinterpret_cast<float2*>(dys)[q * OT + o] = make_float2(v, v);
-                }
-            for (int i = tid; i < tq * GS; i += NT) {
-                const int q = i / GS, rr = i - q * GS;
-                gs[i] = rr < Rspan ? rg[q * Rspan + rr] : 0.f;
-            }
-            for (int i = tid; i < tq * Kspan; i += NT) {
-                const int q = i / Kspan, kk = i - q * Kspan;
-                int k = k_direct ? kk : (f_lo + kk) % K;
-                float acc = raw_dh ? rdh[i] : 0.f;
-                if (k < K && a.dy != nullptr)
-                    for (int o = 0; o < O; ++o) acc = fmaf(rdy[q * O + o], __ldg(a.W + (size_t)k * O + o), acc);
-                dhs[i] = acc;
-            }
-        }
-        __syncthreads();
+        __syncthreads();  // stage landed; everyone is done computing on the other stage
         if (tile + a.splits < ntiles) issue_tile(tile + a.splits, stage ^ 1);
 
-        // ---- hot loop over the queries of the tile ----
-        for (int q = 0; q < tq; ++q) {
-            float2 x2[D];
-            {
-                const float4* xp = reinterpret_cast<const float4*>(xs + (size_t)q * XS);
-#pragma unroll
-                for (int i = 0; i < D / 2; ++i) {
-                    const float4 t = xp[i];
-                    x2[2 * i] = make_float2(t.x, t.y);
-                    x2[2 * i + 1] = make_float2(t.z, t.w);
+        if (!DHT) {
+            // ---- dh table of the tile: dh[q][k] = dy[q,:] . W[k,:] (+ dhidden[q][k]) ----
+            for (int i = tid; i < tq * Kspan; i += NT) {
+                const int q = i / Kspan, kk = i - q * Kspan;
+                const int k = k_direct ? kk : (f_lo + kk) % K;
+                float acc = has_dhid ? sb[st_dh + i] : 0.f;
+                if (k < K && a.dy != nullptr) {
+                    const float* dp = sb + st_dy + (size_t)q * DS;
+                    for (int o = 0; o < O; ++o) acc = fmaf(dp[o], __ldg(a.W + (size_t)k * O + o), acc);
                 }
-                if (D & 1) x2[D - 1] = reinterpret_cast<const float2*>(xs + (size_t)q * XS)[D - 1];
+                dhs[i] = acc;
             }
-            float2 dy2[OTS];
-            if (OT > 0) {
-                const float2* dp = reinterpret_cast<const float2*>(dys + (size_t)q * 2 * OT);
-#pragma unroll
-                for (int o = 0; o < OT; ++o) dy2[o] = dp[o];
-            }
-            const float* gq = gs + (size_t)q * GS;
-            const float* dq = dhs + (size_t)q * Kspan;
-#pragma unroll
-            for (int p = 0; p < NKP; ++p) {
-                const float2 g2 = make_float2(gq[ridx[p][0]], gq[ridx[p][1]]);
-                float2 dh2;
-                if (contig[p]) dh2 = *reinterpret_cast<const float2*>(dq + kidx[p][0]);
-                else dh2 = make_float2(dq[kidx[p][0]], dq[kidx[p][1]]);
-                float2 df[D];
-                df[0] = add2(x2[0], nc2[p][0]);
-                float2 d2 = mul2(df[0], df[0]);
-#pragma unroll
-                for (int j = 1; j < D; ++j) {
-                    df[j] = add2(x2[j], nc2[p][j]);
-                    d2 = fma2(df[j], df[j], d2);
-                }
-                float2 phi;
-                if (BASIS == IRBFN_BASIS_GAUSSIAN) {
-                    const float2 e = mul2(d2, sc2[p]);
-                    phi = make_float2(ex2_approx(e.x), ex2_approx(e.y));
-                } else {
-                    const float2 e = fma2(d2, sc2[p], make_float2(1.f, 1.f));
-                    phi = make_float2(rcp_approx(e.x), rcp_approx(e.y));
-                }
-                const float2 v = mul2(g2, phi);  // gamma * phi
-#pragma unroll
-                for (int o = 0; o < OT; ++o) aW[p][o] = fma2(v, dy2[o], aW[p][o]);
-                float2 t = mul2(v, dh2);         // dh * gamma * phi   (= -dL/d(alpha^2), gaussian)
-                if (BASIS == IRBFN_BASIS_INVERSE_QUADRATIC) t = mul2(t, phi);
-#pragma unroll
-                for (int j = 0; j < D; ++j) aC[p][j] = fma2(t, df[j], aC[p][j]);
-                aL[p] = fma2(t, d2, aL[p]);
-            }
+            __syncthreads();
         }
+
+        // ---- hot loop over the queries of the tile, two at a time for ILP ----
+        int q = 0;
+        for (; q + 1 < tq; q += 2) {
+            eval(sb, q);
+            eval(sb, q + 1);
+        }
+        if (q < tq) eval(sb, q);
+        if (!DHT) __syncthreads();  // the dh table is rebuilt by the next tile
     }
     cp_async_wait_all();
 
@@ -268,35 +290,38 @@ __global__ void __launch_bounds__(256, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
     }
 }
 
-template <int D, int OT, int NKP>
-inline int launch_bwd_p_nkp(const BwdPArgs& a, int basis, int grid, int nt, size_t smem, cudaStream_t st) {
-    cudaError_t e;
-    if (basis == IRBFN_BASIS_GAUSSIAN) {
-        auto kern = irbfn_bwd_p_kernel<D, OT, IRBFN_BASIS_GAUSSIAN, NKP>;
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        kern<<<grid, nt, smem, st>>>(a);
-    } else {
-        auto kern = irbfn_bwd_p_kernel<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, NKP>;
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        kern<<<grid, nt, smem, st>>>(a);
-    }
+// kernel pairs per thread as a function of the output window: keeps the accumulators in registers
+__host__ __device__ constexpr int bwd_p_nkp_for(int OT) { return OT <= 4 ? 2 : 1; }
+
+template <int D, int OT, int BASIS, int DHT>
+inline int launch_bwd_p_inst(const BwdPArgs& a, int grid, int nt, size_t smem, cudaStream_t st) {
+    auto kern = irbfn_bwd_p_kernel<D, OT, BASIS, bwd_p_nkp_for(OT), DHT>;
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<grid, nt, smem, st>>>(a);
     return (int)cudaGetLastError();
 }
 
-// kernel pairs per thread as a function of the output window: keeps the accumulators in registers
-__host__ __device__ constexpr int bwd_p_nkp_for(int OT) { return OT <= 4 ? 3 : (OT <= 10 ? 2 : 1); }
+template <int D, int OT>
+inline int launch_bwd_p_ot(const BwdPArgs& a, int basis, int dht, int grid, int nt, size_t smem, cudaStream_t st) {
+    constexpr int CAN_DHT = (OT == 2 || OT == 4) ? 1 : 0;
+    if (basis == IRBFN_BASIS_GAUSSIAN)
+        return (dht && CAN_DHT) ? launch_bwd_p_inst<D, OT, IRBFN_BASIS_GAUSSIAN, CAN_DHT>(a, grid, nt, smem, st)
+                                : launch_bwd_p_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 0>(a, grid, nt, smem, st);
+    return (dht && CAN_DHT) ? launch_bwd_p_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, CAN_DHT>(a, grid, nt, smem, st)
+                            : launch_bwd_p_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 0>(a, grid, nt, smem, st);
+}
 
 template <int D>
-inline int launch_bwd_p(const BwdPArgs& a, int OT, int basis, int grid, int nt, size_t smem, cudaStream_t st) {
+inline int launch_bwd_p(const BwdPArgs& a, int OT, int basis, int dht, int grid, int nt, size_t smem,
+                        cudaStream_t st) {
     switch (OT) {
-        case 0: return launch_bwd_p_nkp<D, 0, bwd_p_nkp_for(0)>(a, basis, grid, nt, smem, st);
-        case 2: return launch_bwd_p_nkp<D, 2, bwd_p_nkp_for(2)>(a, basis, grid, nt, smem, st);
-        case 4: return launch_bwd_p_nkp<D, 4, bwd_p_nkp_for(4)>(a, basis, grid, nt, smem, st);
-        case 8: return launch_bwd_p_nkp<D, 8, bwd_p_nkp_for(8)>(a, basis, grid, nt, smem, st);
-        case 10: return launch_bwd_p_nkp<D, 10, bwd_p_nkp_for(10)>(a, basis, grid, nt, smem, st);
-        case 16: return launch_bwd_p_nkp<D, 16, bwd_p_nkp_for(16)>(a, basis, grid, nt, smem, st);
+        case 0: return launch_bwd_p_ot<D, 0>(a, basis, dht, grid, nt, smem, st);
+        case 2: return launch_bwd_p_ot<D, 2>(a, basis, dht, grid, nt, smem, st);
+        case 4: return launch_bwd_p_ot<D, 4>(a, basis, dht, grid, nt, smem, st);
+        case 8: return launch_bwd_p_ot<D, 8>(a, basis, dht, grid, nt, smem, st);
+        case 10: return launch_bwd_p_ot<D, 10>(a, basis, dht, grid, nt, smem, st);
+        case 16: return launch_bwd_p_ot<D, 16>(a, basis, dht, grid, nt, smem, st);
         default: return (int)cudaErrorInvalidValue;
     }
 }

@@ -9,8 +9,8 @@
 #define IRBFN_CAT(a, b) IRBFN_CAT_(a, b)
 
 namespace irbfn {
-int IRBFN_CAT(launch_bwd_p_d, IRBFN_D)(const BwdPArgs& a, int OT, int basis, int grid, int nt,
+int IRBFN_CAT(launch_bwd_p_d, IRBFN_D)(const BwdPArgs& a, int OT, int basis, int dht, int grid, int nt,
                                        size_t smem, cudaStream_t st) {
-    return launch_bwd_p<IRBFN_D>(a, OT, basis, grid, nt, smem, st);
+    return launch_bwd_p<IRBFN_D>(a, OT, basis, dht, grid, nt, smem, st);
 }
 }  // namespace irbfn

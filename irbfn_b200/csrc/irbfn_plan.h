@@ -106,21 +106,29 @@ inline bool plan_bwd_x(int R, int K, int D, int OT, int smem_limit, FwdPlan* p) 
 // backward P (parameter gradients): kernel pairs per thread, chunks of pairs per CTA,
 // query splits, tile size.  Must match irbfn_bwd_p.cuh.
 // ---------------------------------------------------------------------------------------
-inline int bwdp_nkp_for(int OT) { return OT <= 4 ? 3 : (OT <= 10 ? 2 : 1); }
+inline int bwdp_nkp_for(int OT) { return OT <= 4 ? 2 : 1; }
+constexpr int kBwdPMaxThreads = 320;   // __launch_bounds__ of irbfn_bwd_p_kernel
 
 struct BwdPPlan {
     int OT, NKP, NT;
     int nchunks, pairs_per_chunk, splits;
     int TQ, Kspan, Rspan;
     int PW;              // partial-sum row width: D + 1 + OT
+    int dht;             // dh formed in-thread from the thread's own readout rows (narrow outputs)
     size_t smem_bytes;
     size_t part_floats;  // splits * R*K * PW
 };
 
-inline size_t bwdp_smem_floats(int TQ, int D, int Dsrc, int O, int OT, int Kspan, int Rspan, int has_dhid) {
-    const size_t raw = (size_t)TQ * (Dsrc + O + Rspan + (has_dhid ? Kspan : 0));
-    return 2 * raw + 4 /*align slack*/ + (size_t)TQ * (((2 * D + 3) / 4) * 4) + (size_t)TQ * 2 * (OT > 0 ? OT : 1) +
-           (size_t)TQ * Kspan + (size_t)TQ * (Rspan + 1);
+// row strides of the shared-memory stage; must match irbfn_bwd_p.cuh
+inline int bwdp_xs_h(int D) { return ((D + 3) / 4) * 4; }
+inline int bwdp_ds_h(int O) { return O <= 0 ? 0 : (O <= 2 ? 2 : ((O + 3) / 4) * 4); }
+
+inline size_t bwdp_smem_floats(int TQ, int D, int O, int Kspan, int Rspan, int has_dhid, int dht) {
+    size_t st = (size_t)TQ * bwdp_xs_h(D) + (size_t)TQ * bwdp_ds_h(O) + (size_t)TQ * (Rspan + 1);
+    st = ((st + 3) / 4) * 4;
+    st += has_dhid ? (size_t)TQ * Kspan : 0;
+    st = ((st + 3) / 4) * 4;
+    return 2 * st + (dht ? 0 : (size_t)TQ * Kspan);
 }
 
 inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT, int has_dhid, int sms,
@@ -129,19 +137,20 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     if (RK <= 0 || RK > (1ll << 30)) return false;
     const int P = (int)((RK + 1) / 2);
     const int NKP = bwdp_nkp_for(OT);
-    const int per_cta = 256 * NKP;
+    const int per_cta = kBwdPMaxThreads * NKP;
     const int nchunks = (P + per_cta - 1) / per_cta;
     const int Pc = (P + nchunks - 1) / nchunks;
     int NT = (((Pc + NKP - 1) / NKP + 31) / 32) * 32;
-    if (NT > 256) NT = 256;
+    if (NT > kBwdPMaxThreads) NT = kBwdPMaxThreads;
     const long long flen = 2ll * Pc;
     int Kspan = flen >= K ? K : (int)flen;
     Kspan = (Kspan + 1) & ~1;
     int Rspan = (int)((flen + K - 1) / K) + 1;
     if (Rspan > R) Rspan = R;
-    int TQ = 64;
-    while (TQ >= 4 && bwdp_smem_floats(TQ, D, Dsrc, O, OT, Kspan, Rspan, has_dhid) * sizeof(float) >
-                          (size_t)smem_limit)
+    (void)Dsrc;
+    const int dht = (!has_dhid && O >= 1 && O <= 4 && (OT == 2 || OT == 4)) ? 1 : 0;
+    int TQ = 256;
+    while (TQ >= 4 && bwdp_smem_floats(TQ, D, O, Kspan, Rspan, has_dhid, dht) * sizeof(float) > (size_t)smem_limit)
         TQ -= 4;
     if (TQ < 4) return false;
     const long long ntiles = (B + TQ - 1) / TQ;
@@ -152,7 +161,8 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     p->nchunks = nchunks; p->pairs_per_chunk = Pc; p->splits = (int)splits;
     p->TQ = TQ; p->Kspan = Kspan; p->Rspan = Rspan;
     p->PW = D + 1 + OT;
-    p->smem_bytes = bwdp_smem_floats(TQ, D, Dsrc, O, OT, Kspan, Rspan, has_dhid) * sizeof(float);
+    p->dht = dht;
+    p->smem_bytes = bwdp_smem_floats(TQ, D, O, Kspan, Rspan, has_dhid, dht) * sizeof(float);
     p->part_floats = (size_t)splits * (size_t)RK * (size_t)p->PW;
     return true;
 }
