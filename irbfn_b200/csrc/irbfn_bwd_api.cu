@@ -397,10 +397,14 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
         a.x = x; a.centers = centers; a.log_sigs = log_sigs; a.W = W; a.gate_ext = gate; a.gd = gdev;
         a.dy = dy_x; a.dhidden = dhid_x;
         a.dx = (grad_mask & IRBFN_GRAD_X) ? dx : nullptr;
+        // tanh gate with few split dims: the kernel folds d gamma into dx itself; otherwise d gamma goes
+        // to the dgate output (external gate) or to scratch for gate_bwd_kernel
+        const bool fuse = gd != nullptr && (grad_mask & IRBFN_GRAD_X) && gdev.S <= BwdXShape::MAX_FUSED_S;
         float* dgbuf = nullptr;
-        if (gd != nullptr && (grad_mask & IRBFN_GRAD_X)) dgbuf = (float*)(ws + L.dgate_off);
+        if (gd != nullptr && (grad_mask & IRBFN_GRAD_X) && !fuse) dgbuf = (float*)(ws + L.dgate_off);
         if (grad_mask & IRBFN_GRAD_GATE) dgbuf = dgate;
         a.dgate = dgbuf;
+        a.fuse_gate = fuse ? 1 : 0;
         a.B = B; a.R = R; a.K = K; a.Dsrc = D; a.O = Ox;
         a.RC = plan.RC; a.KC = plan.KC; a.stage_once = plan.stage_once;
         const long long tiles = (B + BwdXShape::TQ - 1) / BwdXShape::TQ;
@@ -415,7 +419,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             default: e = launch_bwd_x_d8(a, OT, basis, grid, plan.smem_bytes, st); break;
         }
         if (e != 0) return note_cuda_error("irbfn_bwd_x_kernel", e);
-        if (gd != nullptr && (grad_mask & IRBFN_GRAD_X)) {
+        if (gd != nullptr && (grad_mask & IRBFN_GRAD_X) && !fuse) {
             const size_t gsm = (size_t)256 * 2 * gdev.num_bounds * sizeof(float);
             if (gsm > (size_t)smem) return IRBFN_ERR_BAD_GATE;
             if (gsm > 48 * 1024 &&

@@ -4,15 +4,18 @@
 // is autodiff of the forward, model.py:169-198 + flax_rbf.py:275-283, written on d^2 so that
 // x == centre yields the finite analytic limit (F8).
 //
-// Design ("backward kernel X"): the forward's layout -- query-stationary, Q = 4
-// queries per thread as two packed pairs, parameters broadcast from shared-memory records
-// [-c_0,-c_0,...,-c_{D-1},-c_{D-1}, s,s, m,m] with m = -2 exp(-2 log_sig).  With
+// Design: the forward's layout -- query-stationary, Q = 4 queries per thread as two
+// packed pairs, parameters broadcast from transposed 4-kernel shared-memory tiles with rows
+// -c_0 .. -c_{D-1}, s, m  (s the width scale of the basis, m = -2 exp(-2 log_sig)).  With
 //   w = dh_k * gamma_r * dphi/d(alpha^2) * 2 exp(-2 ls)      (per query, region, kernel)
 // the input gradient is dx_j = x_j * sum(w) + sum(w * (-c_j)), so only sum(w) and D packed
-// accumulators are carried and the differences need not stay live.  dh_k = dy . W[k,:] (+dhidden)
-// is formed per kernel tile in registers; d gamma_r = sum_k dh_k phi_rk goes to a thread-private
-// shared-memory column and is either the dgate output (external gate) or, for the tanh gate, is
-// written to scratch and folded into dx by gate_bwd_kernel.
+// accumulators are carried and the differences need not stay live.  Each (kernel tile, region) step
+// is software-pipelined like the forward: its MUFUs are issued during the next step's distance
+// loop, and its w / dx / dgamma updates close that next step.  dh_k = dy . W[k,:] (+dhidden) is formed
+// per kernel tile in registers; d gamma_r = sum_k dh_k phi_rk goes to a thread-private shared-memory
+// column and is either the dgate output (external gate) or, for the tanh gate, folded into dx at
+// the end of the region chunk by the same thread (chain rule through model.py:70-95), so no
+// (B,R) scratch and no second kernel are needed for up to 4 split dimensions.
 #pragma once
 #include "irbfn_common.cuh"
 
@@ -28,36 +31,40 @@ struct BwdXArgs {
     const float* dy;        // (B,O) or nullptr
     const float* dhidden;   // (B,K) or nullptr
     float* dx;              // (B,Dsrc) or nullptr
-    float* dgate;           // (B,R) or nullptr
+    float* dgate;           // (B,R) or nullptr: dgate output, or scratch for gate_bwd_kernel
     long long B;
     int R, K, Dsrc, O;
     int RC, KC;
     int num_tiles;
     int stage_once;
+    int fuse_gate;          // 1: tanh gate, S <= 4: d gamma is folded into dx inside this kernel
 };
 
 struct BwdXShape {
     static constexpr int NT = 256, Q = 4, TQ = NT * Q, KT = 4;
-    static __host__ __device__ constexpr int rec_floats(int D) { return ((2 * D + 4 + 3) / 4) * 4; }
+    static constexpr int MAX_FUSED_S = 4;
+    static __host__ __device__ constexpr int tile_floats(int D) { return (D + 2) * 4; }
 };
 
 template <int D, int OT, int BASIS>
 __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const BwdXArgs a) {
     constexpr int NT = BwdXShape::NT, Q = BwdXShape::Q, TQ = BwdXShape::TQ, KT = BwdXShape::KT;
-    constexpr int RS = BwdXShape::rec_floats(D);
     constexpr int OTS = OT > 0 ? OT : 1;
+    constexpr int TR = D + 2;             // rows per tile
 
     extern __shared__ __align__(16) float smem[];
-    float* stage = smem;                                       // [RC][KC][RS]
-    float* Ws = stage + (size_t)a.RC * a.KC * RS;              // [KC][2*OT]  (w,w) duplicated
-    float* gtab = Ws + (size_t)a.KC * 2 * (OT > 0 ? OT : 0);   // [RC][TQ]
-    float* dgtab = gtab + (size_t)a.RC * TQ;                   // [RC][TQ]
+    const int KCT = a.KC / KT;
+    float4* stage4 = reinterpret_cast<float4*>(smem);              // [RC][KCT][D+2] float4
+    float* stage = smem;
+    float* Ws = smem + (size_t)a.RC * KCT * TR * 4;                // [KC][OT]
+    float* gtab = Ws + (size_t)a.KC * (OT > 0 ? OT : 0);           // [RC][NT] float4
+    float* dgtab = gtab + (size_t)a.RC * TQ;                       // [RC][NT] float4
 
     const int tid = threadIdx.x;
     const int R = a.R, K = a.K, RC = a.RC, KC = a.KC, O = a.O;
     const int n_rch = (R + RC - 1) / RC;
     const int n_kch = (K + KC - 1) / KC;
-    const bool want_dg = a.dgate != nullptr;
+    const bool want_dg = a.dgate != nullptr || a.fuse_gate;
     bool staged = false;
 
     for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
@@ -88,12 +95,15 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
         }
 
         float2 sw[2], dxn[2][D];
+        float4 dxg[BwdXShape::MAX_FUSED_S];   // gate-path contribution to dx_j, j < S (fused gate only)
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
             sw[p] = make_float2(0.f, 0.f);
 #pragma unroll
             for (int j = 0; j < D; ++j) dxn[p][j] = make_float2(0.f, 0.f);
         }
+#pragma unroll
+        for (int j = 0; j < BwdXShape::MAX_FUSED_S; ++j) dxg[j] = make_float4(0.f, 0.f, 0.f, 0.f);
 
         for (int rch = 0; rch < n_rch; ++rch) {
             const int r0 = rch * RC;
@@ -109,13 +119,13 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                     g.y = (q0 + 1 < a.B) ? __ldg(a.gate_ext + (q0 + 1) * R + r0 + rr) : 0.f;
                     g.z = (q0 + 2 < a.B) ? __ldg(a.gate_ext + (q0 + 2) * R + r0 + rr) : 0.f;
                     g.w = (q0 + 3 < a.B) ? __ldg(a.gate_ext + (q0 + 3) * R + r0 + rr) : 0.f;
-                    gcol[rr * (TQ / 4)] = g;
+                    gcol[rr * NT] = g;
                 }
             } else {
                 const int S = a.gd.S;
                 for (int rr = 0; rr < rc; ++rr) {
                     const float one = (r0 + rr < a.gd.num_ranges) ? 1.f : 0.f;
-                    gcol[rr * (TQ / 4)] = make_float4(one, one, one, one);
+                    gcol[rr * NT] = make_float4(one, one, one, one);
                 }
                 const int rlim = min(rc, a.gd.num_ranges - r0);
 #pragma unroll
@@ -132,9 +142,9 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                             f.w = gate_sigmoid(k2, x2[1][j].y - lb) * gate_sigmoid(k2, ub - x2[1][j].y);
                             for (int rr = 0; rr < rlim; ++rr) {
                                 if (__ldg(a.gd.ranges + (r0 + rr) * S + j) == i - ob) {
-                                    float4 g = gcol[rr * (TQ / 4)];
+                                    float4 g = gcol[rr * NT];
                                     g.x *= f.x; g.y *= f.y; g.z *= f.z; g.w *= f.w;
-                                    gcol[rr * (TQ / 4)] = g;
+                                    gcol[rr * NT] = g;
                                 }
                             }
                         }
@@ -142,53 +152,130 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                 }
             }
             if (want_dg)
-                for (int rr = 0; rr < rc; ++rr) dgcol[rr * (TQ / 4)] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int rr = 0; rr < rc; ++rr) dgcol[rr * NT] = make_float4(0.f, 0.f, 0.f, 0.f);
 
             for (int kch = 0; kch < n_kch; ++kch) {
                 const int k0 = kch * KC;
                 const int kc = min(KC, K - k0);
                 const int kcp = ((kc + KT - 1) / KT) * KT;
 
+                // ---- stage parameters, transposed per 4-kernel tile: rows -c_j, s, m ----
                 if (!(a.stage_once && staged)) {
                     __syncthreads();
                     for (int idx = tid; idx < rc * kcp; idx += NT) {
                         const int rr = idx / kcp, kk = idx - rr * kcp;
-                        float* rec = stage + ((size_t)rr * KC + kk) * RS;
+                        float* t = stage + ((size_t)rr * KCT + (kk >> 2)) * (TR * 4) + (kk & 3);
                         if (kk < kc) {
                             const size_t rk = (size_t)(r0 + rr) * K + (k0 + kk);
 #pragma unroll
-                            for (int j = 0; j < D; ++j) {
-                                const float c = j < a.Dsrc ? -__ldg(a.centers + rk * a.Dsrc + j) : 0.f;
-                                rec[2 * j] = c;
-                                rec[2 * j + 1] = c;
-                            }
+                            for (int j = 0; j < D; ++j)
+                                t[4 * j] = j < a.Dsrc ? -__ldg(a.centers + rk * a.Dsrc + j) : 0.f;
                             const float ls = __ldg(a.log_sigs + rk);
-                            const float s = width_scale<BASIS>(ls);
-                            const float m = -2.0f * expf(-2.0f * ls);
-                            rec[2 * D] = s; rec[2 * D + 1] = s;
-                            rec[2 * D + 2] = m; rec[2 * D + 3] = m;
+                            t[4 * D] = width_scale<BASIS>(ls);
+                            t[4 * (D + 1)] = -2.0f * expf(-2.0f * ls);
                         } else {
 #pragma unroll
-                            for (int j = 0; j < 2 * D + 4; ++j) rec[j] = 0.f;
+                            for (int j = 0; j < TR; ++j) t[4 * j] = 0.f;
                         }
-#pragma unroll
-                        for (int j = 2 * D + 4; j < RS; ++j) rec[j] = 0.f;
                     }
                     if (OT > 0) {
                         for (int idx = tid; idx < kcp * OTS; idx += NT) {
                             const int kk = idx / OTS, o = idx - kk * OTS;
-                            const float w = (kk < kc && o < O) ? __ldg(a.W + (size_t)(k0 + kk) * O + o) : 0.f;
-                            Ws[2 * idx] = w;
-                            Ws[2 * idx + 1] = w;
+                            Ws[idx] = (kk < kc && o < O) ? __ldg(a.W + (size_t)(k0 + kk) * O + o) : 0.f;
                         }
                     }
                     __syncthreads();
                     staged = true;
                 }
 
-                for (int kt = 0; kt < kcp; kt += KT) {
-                    // ---- dh for the 4 kernels of the tile x 2 query pairs ----
-                    float2 dh2[KT][2];
+                // ---- hot loop: (kernel tile, region) steps, software-pipelined by one step ----
+                float2 dh2[KT][2], ea[KT][2], ph[KT][2];
+                float2 gp[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+                const float4* recp = stage4;   // tile of the previous step
+                int rrp = 0;                   // region (within the chunk) of the previous step
+                const float kEmpty = BASIS == IRBFN_BASIS_GAUSSIAN ? -INFINITY : INFINITY;  // basis value 0
+#pragma unroll
+                for (int kk = 0; kk < KT; ++kk) {
+                    dh2[kk][0] = dh2[kk][1] = make_float2(0.f, 0.f);
+                    ea[kk][0] = ea[kk][1] = make_float2(kEmpty, kEmpty);
+                }
+
+                auto mufu = [&](int i) {
+                    const int kk = i >> 2, p = (i >> 1) & 1;
+                    float& src = (i & 1) ? ea[kk][p].y : ea[kk][p].x;
+                    float& dst = (i & 1) ? ph[kk][p].y : ph[kk][p].x;
+                    dst = BASIS == IRBFN_BASIS_GAUSSIAN ? ex2_approx(src) : rcp_approx(src);
+                };
+                // d^2 of one step, feature-outer; the previous step's 16 MUFUs ride between the features
+                auto distances = [&](const float4* rec, float2 (&acc)[KT][2]) {
+#pragma unroll
+                    for (int j = 0; j < D; ++j) {
+                        const float4 c4 = rec[j];
+                        const float c[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+                        for (int kk = 0; kk < KT; ++kk) {
+#pragma unroll
+                            for (int p = 0; p < 2; ++p) {
+                                const float2 d = add2(x2[p][j], dup2(c[kk]));
+                                acc[kk][p] = j == 0 ? mul2(d, d) : fma2(d, d, acc[kk][p]);
+                            }
+                        }
+#pragma unroll
+                        for (int i = (16 * j) / D; i < (16 * (j + 1)) / D; ++i) mufu(i);
+                    }
+                };
+                // close the PREVIOUS step: w = dh gamma phi' (2e), dx and d gamma updates
+                auto finish = [&]() {
+                    const float4 m4 = recp[D + 1];
+                    const float m[4] = {m4.x, m4.y, m4.z, m4.w};
+                    float2 wv[KT][2];
+                    float2 dg2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+#pragma unroll
+                    for (int kk = 0; kk < KT; ++kk) {
+#pragma unroll
+                        for (int p = 0; p < 2; ++p) {
+                            dg2[p] = fma2(dh2[kk][p], ph[kk][p], dg2[p]);
+                            float2 w = mul2(mul2(dh2[kk][p], gp[p]), mul2(ph[kk][p], dup2(m[kk])));
+                            if (BASIS == IRBFN_BASIS_INVERSE_QUADRATIC) w = mul2(w, ph[kk][p]);
+                            sw[p] = add2(sw[p], w);
+                            wv[kk][p] = w;
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < D; ++j) {
+                        const float4 c4 = recp[j];
+                        const float c[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+                        for (int kk = 0; kk < KT; ++kk) {
+                            dxn[0][j] = fma2(wv[kk][0], dup2(c[kk]), dxn[0][j]);
+                            dxn[1][j] = fma2(wv[kk][1], dup2(c[kk]), dxn[1][j]);
+                        }
+                    }
+                    if (want_dg) {
+                        float4 d = dgcol[rrp * NT];
+                        d.x += dg2[0].x; d.y += dg2[0].y; d.z += dg2[1].x; d.w += dg2[1].y;
+                        dgcol[rrp * NT] = d;
+                    }
+                };
+                // basis arguments of this step; evaluated during the next step
+                auto scale = [&](const float4* rec, const float2 (&acc)[KT][2], const float4 g4, int rr) {
+                    const float4 s4 = rec[D];
+                    const float sc[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+                    for (int kk = 0; kk < KT; ++kk) {
+#pragma unroll
+                        for (int p = 0; p < 2; ++p) {
+                            if (BASIS == IRBFN_BASIS_GAUSSIAN) ea[kk][p] = mul2(acc[kk][p], dup2(sc[kk]));
+                            else ea[kk][p] = fma2(acc[kk][p], dup2(sc[kk]), make_float2(1.f, 1.f));
+                        }
+                    }
+                    gp[0] = make_float2(g4.x, g4.y);
+                    gp[1] = make_float2(g4.z, g4.w);
+                    recp = rec;
+                    rrp = rr;
+                };
+                // dh of the 4 kernels of tile kt x 2 query pairs
+                auto load_dh = [&](int kt) {
 #pragma unroll
                     for (int kk = 0; kk < KT; ++kk) {
                         dh2[kk][0] = dh2[kk][1] = make_float2(0.f, 0.f);
@@ -204,71 +291,93 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                             }
                         }
                         if (OT > 0) {
-                            const float2* w2 = reinterpret_cast<const float2*>(Ws + (size_t)(kt + kk) * 2 * OTS);
+                            const float* wr = Ws + (size_t)(kt + kk) * OTS;
 #pragma unroll
                             for (int o = 0; o < OT; ++o) {
-                                const float2 wv = w2[o];
-                                dh2[kk][0] = fma2(dy2[0][o], wv, dh2[kk][0]);
-                                dh2[kk][1] = fma2(dy2[1][o], wv, dh2[kk][1]);
+                                const float w = wr[o];
+                                dh2[kk][0] = fma2(dy2[0][o], dup2(w), dh2[kk][0]);
+                                dh2[kk][1] = fma2(dy2[1][o], dup2(w), dh2[kk][1]);
                             }
                         }
                     }
+                };
 
-                    for (int rr = 0; rr < rc; ++rr) {
-                        const float4 g4 = gcol[rr * (TQ / 4)];
-                        const float2 g2[2] = {make_float2(g4.x, g4.y), make_float2(g4.z, g4.w)};
-                        float2 dg2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
-                        const float4* rec4 =
-                            reinterpret_cast<const float4*>(stage + ((size_t)rr * KC + kt) * RS);
-#pragma unroll
-                        for (int kk = 0; kk < KT; ++kk) {
-                            float v[RS];
-#pragma unroll
-                            for (int i = 0; i < RS / 4; ++i) {
-                                const float4 t = rec4[kk * (RS / 4) + i];
-                                v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-                            }
-                            const float2 sc = make_float2(v[2 * D], v[2 * D + 1]);
-                            const float2 m2 = make_float2(v[2 * D + 2], v[2 * D + 3]);
-#pragma unroll
-                            for (int p = 0; p < 2; ++p) {
-                                float2 t = add2(x2[p][0], make_float2(v[0], v[1]));
-                                float2 acc = mul2(t, t);
-#pragma unroll
-                                for (int j = 1; j < D; ++j) {
-                                    t = add2(x2[p][j], make_float2(v[2 * j], v[2 * j + 1]));
-                                    acc = fma2(t, t, acc);
-                                }
-                                float2 phi;
-                                if (BASIS == IRBFN_BASIS_GAUSSIAN) {
-                                    const float2 e = mul2(acc, sc);
-                                    phi = make_float2(ex2_approx(e.x), ex2_approx(e.y));
-                                } else {
-                                    const float2 e = fma2(acc, sc, make_float2(1.f, 1.f));
-                                    phi = make_float2(rcp_approx(e.x), rcp_approx(e.y));
-                                }
-                                dg2[p] = fma2(dh2[kk][p], phi, dg2[p]);
-                                // w = dh * gamma * dphi/d(alpha^2) * 2 e  = dh gamma phi (-2e)  [* phi for IQ]
-                                float2 w = mul2(mul2(dh2[kk][p], g2[p]), mul2(phi, m2));
-                                if (BASIS == IRBFN_BASIS_INVERSE_QUADRATIC) w = mul2(w, phi);
-                                sw[p] = add2(sw[p], w);
-#pragma unroll
-                                for (int j = 0; j < D; ++j)
-                                    dxn[p][j] = fma2(w, make_float2(v[2 * j], v[2 * j + 1]), dxn[p][j]);
-                            }
-                        }
-                        if (want_dg) {
-                            float4 d = dgcol[rr * (TQ / 4)];
-                            d.x += dg2[0].x; d.y += dg2[0].y; d.z += dg2[1].x; d.w += dg2[1].y;
-                            dgcol[rr * (TQ / 4)] = d;
-                        }
+                const size_t rstride = (size_t)KCT * TR;
+                for (int kt = 0; kt < kcp; kt += KT) {
+                    const float4* rec = stage4 + (size_t)(kt >> 2) * TR;
+                    {   // first region of the tile (peeled): the previous step belongs to tile kt - KT,
+                        // so it is closed with the OLD dh before the new one is formed
+                        const float4 g4 = gcol[0];
+                        float2 acc[KT][2];
+                        distances(rec, acc);
+                        finish();
+                        load_dh(kt);
+                        scale(rec, acc, g4, 0);
+                    }
+                    for (int rr = 1; rr < rc; ++rr) {   // branch-free steady state
+                        rec += rstride;
+                        const float4 g4 = gcol[rr * NT];
+                        float2 acc[KT][2];
+                        distances(rec, acc);
+                        finish();
+                        scale(rec, acc, g4, rr);
                     }
                 }
+                // drain the pipeline
+#pragma unroll
+                for (int i = 0; i < 16; ++i) mufu(i);
+                finish();
             }
 
-            if (want_dg) {
+            if (a.fuse_gate) {
+                // ---- dx_j += sum_r dgamma_r * d gamma_r / d x_j   (tanh gate, model.py:70-95) ----
+                // s(z) = 1/(1+exp(-2 delta z)):  f = s(x-lb) s(ub-x),  f' = 2 delta f (s(ub-x) - s(x-lb))
+                const int S = a.gd.S;
+                const int rlim = min(rc, a.gd.num_ranges - r0);
+                for (int rr = 0; rr < rlim; ++rr) {
+                    const float4 dgv = dgcol[rr * NT];
+                    float4 f[BwdXShape::MAX_FUSED_S], fd[BwdXShape::MAX_FUSED_S];
+#pragma unroll
+                    for (int j = 0; j < BwdXShape::MAX_FUSED_S; ++j) {
+                        f[j] = make_float4(1.f, 1.f, 1.f, 1.f);
+                        fd[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (j < S) {
+                            const float dl = __ldg(a.gd.delta + j);
+                            const float k2 = 2.0f * kLog2e * dl;
+                            const int i = __ldg(a.gd.offset + j) + __ldg(a.gd.ranges + (r0 + rr) * S + j);
+                            const float lb = __ldg(a.gd.lower + i), ub = __ldg(a.gd.upper + i);
+                            const float xq[4] = {x2[0][j].x, x2[0][j].y, x2[1][j].x, x2[1][j].y};
+                            float fv[4], fdv[4];
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const float sl = gate_sigmoid(k2, xq[q] - lb), su = gate_sigmoid(k2, ub - xq[q]);
+                                fv[q] = sl * su;
+                                fdv[q] = 2.0f * dl * sl * su * (su - sl);
+                            }
+                            f[j] = make_float4(fv[0], fv[1], fv[2], fv[3]);
+                            fd[j] = make_float4(fdv[0], fdv[1], fdv[2], fdv[3]);
+                        }
+                    }
+                    float4 pre[BwdXShape::MAX_FUSED_S];
+                    float4 run = make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll
+                    for (int j = 0; j < BwdXShape::MAX_FUSED_S; ++j) {
+                        pre[j] = run;
+                        run.x *= f[j].x; run.y *= f[j].y; run.z *= f[j].z; run.w *= f[j].w;
+                    }
+                    run = dgv;
+#pragma unroll
+                    for (int j = BwdXShape::MAX_FUSED_S - 1; j >= 0; --j) {
+                        dxg[j].x = fmaf(fd[j].x * pre[j].x, run.x, dxg[j].x);
+                        dxg[j].y = fmaf(fd[j].y * pre[j].y, run.y, dxg[j].y);
+                        dxg[j].z = fmaf(fd[j].z * pre[j].z, run.z, dxg[j].z);
+                        dxg[j].w = fmaf(fd[j].w * pre[j].w, run.w, dxg[j].w);
+                        run.x *= f[j].x; run.y *= f[j].y; run.z *= f[j].z; run.w *= f[j].w;
+                    }
+                }
+            } else if (a.dgate != nullptr) {
                 for (int rr = 0; rr < rc; ++rr) {
-                    const float4 d = dgcol[rr * (TQ / 4)];
+                    const float4 d = dgcol[rr * NT];
                     if (q0 + 0 < a.B) a.dgate[(q0 + 0) * R + r0 + rr] = d.x;
                     if (q0 + 1 < a.B) a.dgate[(q0 + 1) * R + r0 + rr] = d.y;
                     if (q0 + 2 < a.B) a.dgate[(q0 + 2) * R + r0 + rr] = d.z;
@@ -277,14 +386,18 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
             }
         }
 
-        // ---- dx_j = x_j * sum(w) + sum(w * -c_j) ----
+        // ---- dx_j = x_j * sum(w) + sum(w * -c_j)  (+ the gate path) ----
         if (a.dx != nullptr) {
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
                 const long long qa = q0 + 2 * p, qb = qa + 1;
 #pragma unroll
                 for (int j = 0; j < D; ++j) {
-                    const float2 r = fma2(x2[p][j], sw[p], dxn[p][j]);
+                    float2 r = fma2(x2[p][j], sw[p], dxn[p][j]);
+                    if (j < BwdXShape::MAX_FUSED_S) {
+                        r.x += p == 0 ? dxg[j].x : dxg[j].z;
+                        r.y += p == 0 ? dxg[j].y : dxg[j].w;
+                    }
                     if (j < a.Dsrc) {
                         if (qa < a.B) a.dx[qa * a.Dsrc + j] = r.x;
                         if (qb < a.B) a.dx[qb * a.Dsrc + j] = r.y;

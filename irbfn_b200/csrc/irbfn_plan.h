@@ -70,17 +70,18 @@ inline bool plan_forward(int R, int K, int D, int OT, int smem_limit, FwdPlan* p
 // ---------------------------------------------------------------------------------------
 // backward X (query-side): same staging scheme as the forward, wider records, two gate tables
 // ---------------------------------------------------------------------------------------
-inline int bwdx_rec_floats(int D) { return ((2 * D + 4 + 3) / 4) * 4; }
+inline int bwdx_tile_floats(int D) { return (D + 2) * 4; }   // rows -c_0..-c_{D-1}, s, m of 4 kernels
 
+// stage [RC][KC/4] tiles + readout rows [KC][OT] + gate and d-gate tables [RC][1024] each
 inline size_t bwdx_smem_bytes(int RC, int KC, int D, int OT) {
-    return ((size_t)RC * KC * bwdx_rec_floats(D) + (size_t)KC * 2 * OT + (size_t)2 * RC * kFwdTQ) *
+    return ((size_t)RC * (KC / kFwdKT) * bwdx_tile_floats(D) + (size_t)KC * OT + (size_t)2 * RC * kFwdTQ) *
            sizeof(float);
 }
 
 inline bool plan_bwd_x(int R, int K, int D, int OT, int smem_limit, FwdPlan* p) {
     const int Kp = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
     if (bwdx_smem_bytes(R, Kp, D, OT) <= (size_t)smem_limit) {
-        *p = FwdPlan{R, Kp, 1, bwdx_smem_bytes(R, Kp, D, OT)};
+        *p = FwdPlan{R, Kp, 1, bwdx_smem_bytes(R, Kp, D, OT), 256};
         return true;
     }
     const int want = Kp < 64 ? Kp : 64;
@@ -90,12 +91,12 @@ inline bool plan_bwd_x(int R, int K, int D, int OT, int smem_limit, FwdPlan* p) 
         if (RC <= 0) continue;
         const size_t fixed = (size_t)2 * RC * kFwdTQ * sizeof(float);
         if (fixed >= (size_t)smem_limit) continue;
-        const size_t per_k = ((size_t)RC * bwdx_rec_floats(D) + 2 * OT) * sizeof(float);
+        const size_t per_k = ((size_t)RC * bwdx_tile_floats(D) / kFwdKT + OT) * sizeof(float);
         long long KC = (long long)(((size_t)smem_limit - fixed) / per_k);
         KC = (KC / kFwdKT) * kFwdKT;
         if (KC > Kp) KC = Kp;
         if (KC >= want || (RC == 1 && KC >= kFwdKT)) {
-            *p = FwdPlan{RC, (int)KC, 0, bwdx_smem_bytes(RC, (int)KC, D, OT)};
+            *p = FwdPlan{RC, (int)KC, 0, bwdx_smem_bytes(RC, (int)KC, D, OT), 256};
             return true;
         }
     }
