@@ -156,6 +156,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extras", action="store_true", help="skip the train-step / input-gradient side measurements")
+    ap.add_argument("--no-other", action="store_true", help="skip the C1 / C2b / C5 side measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -339,6 +340,111 @@ def extras(net, params, cfg, dev, world, args):
     res["input_grad_C4"] = {"queries_per_gpu": B4, "scaling": "weak", "ms_vjp_dx": ms4,
                             "queries_per_s": world * B4 / (ms4 * 1e-3),
                             "algorithmic_tflops": (R * K * (5 * D + 7) + 2 * K * O) * B4 / (ms4 * 1e-3) / 1e12}
+    # 8f rank 2: one-pass Jacobian dy/dx (B,O,D) on the C4 queries, against O one-hot VJP launches (jacrev)
+    W_, b_ = p["linear"]["kernel"], p["linear"]["bias"]
+    msj = timed(lambda: ops.jacobian(x4, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], W_, gd=gd, basis=0),
+                max(3, args.steps // 2), 3)
+    res["jacobian_8f2"] = {"queries_per_gpu": B4, "ms_one_pass": msj, "ms_jacrev_equivalent": O * ms4,
+                           "queries_per_s": world * B4 / (msj * 1e-3),
+                           "lane_ops_T_per_s": (R * K * (2 * D + 3 + O * (D + 2))) * B4 / (msj * 1e-3) / 1e12}
+    # 8f rank 1: the same C3 step with the reference's Frenet one-step dynamics loss fused in
+    ms_d = timed(lambda: grad_step(state, x, y, GB, loss="frenet_oneint"), args.steps, args.warmup)
+    res["train_step_C3_frenet_dynamics_loss"] = {"global_batch": GB, "ms_fwd_loss_vjp_allreduce": ms_d,
+                                                 "samples_per_s": GB / (ms_d * 1e-3)}
+    xl, yl, ypl = x4[:, :8].contiguous(), torch.randn((B4, 10), device=dev), torch.randn((B4, 10), device=dev)
+    ms_l = timed(lambda: ops.dynamics_loss(1, xl, ypl, yl, state.dyn_params), args.steps, 3)
+    res["dynamics_loss_fullint_8f1"] = {"samples": B4, "ms": ms_l, "hbm_GBps": B4 * 4 * (8 + 30) / (ms_l * 1e-3) / 1e9,
+                                        "note": "five-step Frenet rollout x2 + adjoint, 152 B/sample"}
+    if not args.no_other:
+        res.update(other_configs(dev, world, args, timed))
+    return res
+
+
+def _fixture(name):
+    z = np.load(os.path.join(ROOT, "tests", "golden", name))
+    cfg = json.loads(str(z["cfg_json"]))
+    p = {"centers": z["p/rbf_list/centers"], "log_sigs": z["p/rbf_list/log_sigs"],
+         "kernel": z["p/linear/kernel"], "bias": z["p/linear/bias"]}
+    return cfg, p
+
+
+def other_configs(dev, world, args, timed):
+    """The remaining BASELINE.json configs, measured with the same discipline:
+    C1 (4,096-query call, latency-bound), C2b (readout-heavy 1 x 1000 x 8 -> 10 on the 2^20 lattice)
+    and C5 (64 local networks x 4,096 centres, 6-D, 16 outputs, 2^24 queries per GPU; parameters
+    larger than shared memory, so the kernels walk (region, kernel) stages)."""
+    import torch
+    from irbfn_b200 import ops
+    res = {}
+    to = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(dev)
+
+    def module(cfg, p):
+        gd = ops.GatePack(cfg["lower_bounds"], cfg["upper_bounds"], cfg["delta"], cfg["dimension_ranges"], dev)
+        return gd, [to(p[k]) for k in ("centers", "log_sigs", "kernel", "bias")]
+
+    # C1: one 4,096-query call on the Cartesian NMPC shape; launch latency dominates 1.5 us of math
+    cfg, p = _fixture("c1_cartesian_1x1000.npz")
+    gd, (c, ls, W, b) = module(cfg, p)
+    lo = np.array([min(v) for v in cfg["lower_bounds"]], np.float32)
+    hi = np.array([max(v) for v in cfg["upper_bounds"]], np.float32)
+    x1 = to(np.random.default_rng(0).uniform(lo, hi, (4096, len(lo))))
+    y1 = torch.empty((4096, cfg["out_features"]), device=dev)
+    ms1 = timed(lambda: ops.forward(x1, c, ls, W, b, gd=gd, basis=0, out=y1), 200, 20)
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream(dev)
+    with torch.cuda.stream(s):
+        ops.forward(x1, c, ls, W, b, gd=gd, basis=0, out=y1)
+        with torch.cuda.graph(g, stream=s):
+            for _ in range(20):
+                ops.forward(x1, c, ls, W, b, gd=gd, basis=0, out=y1)
+    torch.cuda.synchronize()
+    ms1g = timed(g.replay, 20, 3) / 20
+    res["forward_C1"] = {"queries": 4096, "shape": "R1_K1000_D7_O2_gaussian", "us_per_call": ms1 * 1e3,
+                         "us_per_call_in_cuda_graph": ms1g * 1e3, "queries_per_s": 4096 / (ms1 * 1e-3),
+                         "queries_per_s_in_cuda_graph": 4096 / (ms1g * 1e-3)}
+
+    # C2b: readout share 43 %
+    cfg, p = _fixture("c2b_frenet_1x1000_o10.npz")
+    gd, (c, ls, W, b) = module(cfg, p)
+    xb = to(np.random.default_rng(1).uniform([min(v) for v in cfg["lower_bounds"]],
+                                             [max(v) for v in cfg["upper_bounds"]], (B_LATTICE, 8)))
+    yb = torch.empty((B_LATTICE, 10), device=dev)
+    msb = timed(lambda: ops.forward(xb, c, ls, W, b, gd=gd, basis=0, out=yb), args.steps, 3)
+    lane = 1000 * (2 * 8 + 2) + 1000 * 10
+    res["forward_C2b"] = {"queries_per_gpu": B_LATTICE, "shape": "R1_K1000_D8_O10_gaussian", "ms": msb,
+                          "queries_per_s": world * B_LATTICE / (msb * 1e-3),
+                          "lane_ops_T_per_s": lane * B_LATTICE / (msb * 1e-3) / 1e12}
+    del xb, yb
+
+    # C5: stress shape, synthetic parameters (seed 1234), 4 x 4 x 4 regions on dims 0-2 over [-1,1]
+    R, K, D, O = 64, 4096, 6, 16
+    rng = np.random.default_rng(1234)
+    edges = np.linspace(-1.0, 1.0, 5)
+    lbs = [list(edges[:-1])] * 3
+    ubs = [list(edges[1:])] * 3
+    ranges = [[i, j, k] for i in range(4) for j in range(4) for k in range(4)]
+    gd5 = ops.GatePack(lbs, ubs, [100.0] * 3, ranges, dev)
+    c5 = to(rng.uniform(-1, 1, (R, K, D)))
+    ls5 = to(rng.uniform(0, 2, (R, K)))
+    W5 = to(rng.standard_normal((K, O)))
+    b5 = torch.zeros(O, device=dev)
+    B5 = 1 << 24
+    x5 = torch.rand((B5, D), device=dev) * 2 - 1
+    y5 = torch.empty((B5, O), device=dev)
+    ms5 = timed(lambda: ops.forward(x5, c5, ls5, W5, b5, gd=gd5, basis=0, out=y5), 2, 1)
+    lane5 = R * K * (2 * D + 2) + K * O
+    res["forward_C5"] = {"queries_per_gpu": B5, "shape": "R64_K4096_D6_O16_gaussian", "ms": ms5,
+                         "queries_per_s": world * B5 / (ms5 * 1e-3),
+                         "lane_ops_T_per_s": lane5 * B5 / (ms5 * 1e-3) / 1e12, "timed_steps": 2, "warmup": 1}
+    B5b = 1 << 22
+    dy5 = torch.randn((B5b, O), device=dev)
+    flat = torch.empty(R * K * (D + 1) + K * O + O, device=dev)
+    ms5b = timed(lambda: (ops.forward(x5[:B5b], c5, ls5, W5, b5, gd=gd5, basis=0, out=y5[:B5b]),
+                          ops.backward(x5[:B5b], c5, ls5, W5, dy5, gd=gd5, basis=0, grad_mask=ops.GRAD_PARAMS,
+                                       flat_out=flat)), 2, 1)
+    res["fwd_vjp_C5"] = {"queries_per_gpu": B5b, "ms": ms5b, "queries_per_s": world * B5b / (ms5b * 1e-3),
+                         "algorithmic_tflops": (R * K * (3 * D + 2) + R * K * (5 * D + 9) + 6 * K * O) * B5b
+                                               / (ms5b * 1e-3) / 1e12, "timed_steps": 2, "warmup": 1}
     return res
 
 

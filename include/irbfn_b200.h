@@ -180,6 +180,72 @@ int irbfn_fp32_microbench(int mode, int iters, int blocks, float* scratch,
 int irbfn_pipe_microbench(int mode, int iters, int blocks, float* scratch, double* rates,
                           float* elapsed_ms, irbfn_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Loss-side vehicle dynamics: the tail of the reference's loss_fn after
+ * wcrbf.apply, fused into one launch that yields the loss terms AND the cotangent dloss/dy_pred
+ * which irbfn_backward consumes.
+ *
+ *   mode IRBFN_LOSS_FRENET_ONEINT  <- train_step_oneint   scripts/train_nmpc_frenet.py:339-392
+ *                                     (|y_pred - y|.mean() + 100 |aux(x,y_pred) - aux(x,y)|.mean(),
+ *                                      aux = dynamic_frenet_onestep_aux, dynamics.py:293-383)
+ *   mode IRBFN_LOSS_FRENET_FULLINT <- train_step_fullint  scripts/train_nmpc_frenet.py:395-420
+ *                                     (integrate_frenet_mult, dynamics.py:284-290; O == 10)
+ *   mode IRBFN_LOSS_ST_ONEINT      <- train_step_oneint   scripts/train_nmpc.py:258-300
+ *                                     (optax.l2_loss terms; dynamic_st_onestep_aux, dynamics.py:103-187)
+ *   mode IRBFN_LOSS_ST_FULLINT     <- train_step_fullint  scripts/train_nmpc.py:303-421 (O == 10)
+ *
+ *   x (B,D), y_pred (B,O), y (B,O) device; dyn_params: HOST array of 13 floats in the order of
+ *   scripts/train_nmpc_frenet.py:322-338 (mu, m, I, lf, lr, C_Sf, C_Sr, h, dt, sv_max, a_max,
+ *   s_max, v_max).  O is 2 or 10.  Means are taken over global_batch (>= B) samples so that shard
+ *   cotangents / losses summed over ranks equal the one-device values.
+ *   dy (B,O) device out; losses device out, 2 floats: {pred_loss, int_loss (weighted)} of this shard.
+ *   Reduction is deterministic (fixed partition, fixed order, fp64).
+ */
+#define IRBFN_LOSS_FRENET_ONEINT 0
+#define IRBFN_LOSS_FRENET_FULLINT 1
+#define IRBFN_LOSS_ST_ONEINT 2
+#define IRBFN_LOSS_ST_FULLINT 3
+
+size_t irbfn_dynamics_loss_workspace_bytes(int64_t B);
+
+int irbfn_dynamics_loss(int mode, const float* x, const float* y_pred, const float* y,
+                        const float* dyn_params, float* dy, float* losses, int64_t B, int D, int O,
+                        int64_t global_batch, void* workspace, size_t workspace_bytes,
+                        irbfn_stream_t stream);
+
+/*
+ * Plain rollouts (what irbfn_planner.py:212-214,510-518 and the losses call):
+ *   IRBFN_DYN_FRENET_MULT         integrate_frenet_mult       dynamics.py:284-290  (B,18) -> (B,5,8)
+ *   IRBFN_DYN_FRENET_ONESTEP_AUX  dynamic_frenet_onestep_aux  dynamics.py:293-383  (B,width>=8) -> (B,6)
+ *   IRBFN_DYN_ST_MULT             integrate_st_mult           dynamics.py:94-100   (B,17) -> (B,5,7)
+ *   IRBFN_DYN_ST_ONESTEP_AUX      dynamic_st_onestep_aux      dynamics.py:103-187  (B,width>=9) -> (B,7)
+ * x_and_u (B,width) and states are device arrays; dyn_params is a HOST array of 13 floats.
+ */
+#define IRBFN_DYN_FRENET_MULT 0
+#define IRBFN_DYN_FRENET_ONESTEP_AUX 1
+#define IRBFN_DYN_ST_MULT 2
+#define IRBFN_DYN_ST_ONESTEP_AUX 3
+
+int irbfn_integrate(int model, const float* x_and_u, const float* dyn_params, float* states,
+                    int64_t B, int width, irbfn_stream_t stream);
+
+/*
+ * Per-query Jacobian in one pass:  jac[b,o,j] = d y[b,o] / d x[b,j].
+ * Replaces jax.jacrev(lambda x: model.apply(params, x)) over WCRBFNet.__call__
+ * (src/irbfn_mpc/model.py:169-198); the reference has no call site.
+ *   jac      (B,O,D)  out
+ *   y        (B,O)    out or NULL (the forward value rides along for free)
+ *   region_y (B,R,O)  out or NULL: sum_k W[k,o] phi_rk per region.  With an external gate the
+ *                     Jacobian holds the RBF-layer term only (gate treated as constant); the caller
+ *                     adds sum_r region_y[b,r,o] * dgate[b,r]/dx_j.  With the tanh gate (gd) the
+ *                     gate's own dependence on x is included.
+ * Other arguments as irbfn_forward.  No workspace.
+ */
+int irbfn_jacobian(const float* x, const float* centers, const float* log_sigs, const float* W,
+                   const float* bias, const float* gate, const IrbfnGateDesc* gd, float* jac,
+                   float* y, float* region_y, int64_t B, int R, int K, int D, int O, int basis,
+                   irbfn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,11 +25,15 @@ GRAD_PARAMS = GRAD_CENTERS | GRAD_LOG_SIGS | GRAD_KERNEL
 
 ABI_VERSION = 1
 
+LOSS_FRENET_ONEINT, LOSS_FRENET_FULLINT, LOSS_ST_ONEINT, LOSS_ST_FULLINT = 0, 1, 2, 3
+DYN_FRENET_MULT, DYN_FRENET_ONESTEP_AUX, DYN_ST_MULT, DYN_ST_ONESTEP_AUX = 0, 1, 2, 3
+
 # every symbol include/irbfn_b200.h declares (tests check the .so exports exactly these)
 EXPORTED_SYMBOLS = (
     "irbfn_abi_version", "irbfn_error_string", "irbfn_last_error_detail", "irbfn_forward_workspace_bytes", "irbfn_forward",
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_fp32_microbench", "irbfn_pipe_microbench", "irbfn_forward_plan",
+    "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
 )
 
 
@@ -89,6 +93,14 @@ def load():
     lib.irbfn_forward_plan.argtypes = [i, i, i, i, i, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(sz)]
     lib.irbfn_pipe_microbench.restype = i
     lib.irbfn_pipe_microbench.argtypes = [i, i, i, p, C.POINTER(C.c_double), C.POINTER(C.c_float), p]
+    lib.irbfn_dynamics_loss_workspace_bytes.restype = sz
+    lib.irbfn_dynamics_loss_workspace_bytes.argtypes = [i64]
+    lib.irbfn_dynamics_loss.restype = i
+    lib.irbfn_dynamics_loss.argtypes = [i, p, p, p, C.POINTER(C.c_float), p, p, i64, i, i, i64, p, sz, p]
+    lib.irbfn_integrate.restype = i
+    lib.irbfn_integrate.argtypes = [i, p, C.POINTER(C.c_float), p, i64, i, p]
+    lib.irbfn_jacobian.restype = i
+    lib.irbfn_jacobian.argtypes = [p, p, p, p, p, p, C.POINTER(GateDesc), p, p, p, i64, i, i, i, i, i, p]
     if lib.irbfn_abi_version() != ABI_VERSION:
         raise ImportError("libirbfn_b200.so ABI %d != binding ABI %d"
                           % (lib.irbfn_abi_version(), ABI_VERSION))

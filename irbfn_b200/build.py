@@ -30,13 +30,14 @@ FEATURE_COUNTS = (4, 5, 6, 7, 8)
 
 
 def _units():
-    units = [("irbfn_api.cu", [], "irbfn_api.o"), ("fp32_peak.cu", [], "fp32_peak.o")]
-    for name in ("irbfn_fwd_inst.cu", "irbfn_bwd_x_inst.cu", "irbfn_bwd_p_inst.cu"):
+    units = [("irbfn_api.cu", [], "irbfn_api.o"), ("fp32_peak.cu", [], "fp32_peak.o"),
+             ("irbfn_dynamics.cu", [], "irbfn_dynamics.o")]
+    for name in ("irbfn_fwd_inst.cu", "irbfn_bwd_x_inst.cu", "irbfn_bwd_p_inst.cu", "irbfn_jac_inst.cu"):
         if not os.path.exists(os.path.join(CSRC, name)):
             continue
         for d in FEATURE_COUNTS:
             units.append((name, ["-DIRBFN_D=%d" % d], "%s_d%d.o" % (name[:-3], d)))
-    for name in ("irbfn_bwd_api.cu",):
+    for name in ("irbfn_bwd_api.cu", "irbfn_jac_api.cu"):
         if os.path.exists(os.path.join(CSRC, name)):
             units.append((name, [], name[:-3] + ".o"))
     return units

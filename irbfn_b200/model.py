@@ -271,6 +271,19 @@ class WCRBFNet(_IrbfnModule):
         return _IrbfnFunction.apply(xd, centers, log_sigs, kernel, bias, None, self._gate_pack(device),
                                     self._basis, False)
 
+    def jacobian(self, params, x, with_value: bool = False):
+        """jax.vmap(jax.jacrev(lambda q: self.apply(params, q[None])[0]))(x): (B, O, D), one pass
+        (SURVEY.md 8f rank 2).  ``with_value`` also returns y (B, O) from the same launch."""
+        device = self._device_of(x)
+        p = _unwrap(params)
+        xd = self._prep_x(x, device)
+        if xd is None:
+            xd = _leaf(x, device)
+        centers, log_sigs = self._rbf_leaves(p, device)
+        kernel, bias = _leaf(p["linear"]["kernel"], device), _leaf(p["linear"]["bias"], device)
+        return ops.jacobian(xd, centers, log_sigs, kernel, bias, gd=self._gate_pack(device), basis=self._basis,
+                            want_y=with_value)
+
     def apply_host(self, params, x, out=None, chunk: int = 1 << 17):
         """Host-buffer entry point: x is a NumPy array or CPU tensor (B,D); the batch is cut into
         chunks whose host->device copy, kernel and device->host copy overlap on three streams.

@@ -18,6 +18,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
 
 __all__ = [
     "GatePack", "forward", "backward", "region_gate", "softmax_gate", "fp32_microbench", "pipe_microbench",
+    "dynamics_loss", "integrate", "default_dyn_params", "jacobian",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
     "GRAD_X", "GRAD_GATE", "GRAD_PARAMS",
 ]
@@ -257,3 +258,101 @@ def pipe_microbench(mode: int, iters: int = 20000, blocks: Optional[int] = None,
         rc = lib.irbfn_pipe_microbench(mode, iters, blocks, _ptr(scratch), rates, C.byref(ms), _stream())
     _lib.check(rc, "irbfn_pipe_microbench")
     return rates[0], rates[1], rates[2], ms.value
+
+
+# --------------------------------------------------------------------------- loss-side dynamics
+def default_dyn_params(mu: float = 1.0489, cs: float = 4.718):
+    """dyn_params of the reference's training scripts (scripts/train_nmpc_frenet.py:322-338):
+    [mu, m, I, lf, lr, C_Sf, C_Sr, h, dt, sv_max, a_max, s_max, v_max]."""
+    return [mu, 1.0489, 0.04712, 0.15875, 0.17145, cs, cs, 0.074, 0.1, 3.2, 9.51, 0.4189, 7.0]
+
+
+def _dyn_array(dyn_params):
+    v = [float(t) for t in dyn_params]
+    if len(v) != 13:
+        raise ValueError("dyn_params must hold 13 values")
+    return (C.c_float * 13)(*v)
+
+
+def dynamics_loss(mode: int, x, y_pred, y, dyn_params, global_batch: Optional[int] = None,
+                  dy: Optional[torch.Tensor] = None, losses: Optional[torch.Tensor] = None):
+    """Fused loss tail of the reference's training steps (irbfn_dynamics_loss): returns
+    (losses, dy) with losses = device tensor [pred_loss, int_loss] of this shard (means over
+    ``global_batch``) and dy = dloss/dy_pred (B,O)."""
+    lib = _lib.load()
+    _chk(x, "x")
+    _chk(y_pred, "y_pred")
+    B, D = x.shape
+    O = y_pred.shape[1]
+    _chk(y_pred, "y_pred", (B, O))
+    _chk(y, "y", (B, O))
+    gb = int(global_batch) if global_batch is not None else B
+    dy = dy if dy is not None else torch.empty((B, O), device=x.device, dtype=torch.float32)
+    losses = losses if losses is not None else torch.empty(2, device=x.device, dtype=torch.float32)
+    _chk(dy, "dy", (B, O))
+    _chk(losses, "losses", (2,))
+    with torch.cuda.device(x.device):
+        nbytes = lib.irbfn_dynamics_loss_workspace_bytes(B)
+        ws = _workspace(nbytes, x.device)
+        rc = lib.irbfn_dynamics_loss(mode, _ptr(x), _ptr(y_pred), _ptr(y), _dyn_array(dyn_params), _ptr(dy),
+                                     _ptr(losses), B, D, O, gb, _ptr(ws), nbytes, _stream())
+    _lib.check(rc, "irbfn_dynamics_loss")
+    return losses, dy
+
+
+_DYN_OUT = {_lib.DYN_FRENET_MULT: (5, 8), _lib.DYN_FRENET_ONESTEP_AUX: (6,), _lib.DYN_ST_MULT: (5, 7),
+            _lib.DYN_ST_ONESTEP_AUX: (7,)}
+
+
+def integrate(model: int, x_and_u, dyn_params):
+    """integrate_frenet_mult / dynamic_frenet_onestep_aux / integrate_st_mult /
+    dynamic_st_onestep_aux of the reference's dynamics.py on the device (irbfn_integrate)."""
+    lib = _lib.load()
+    _chk(x_and_u, "x_and_u")
+    if model not in _DYN_OUT:
+        raise ValueError("unknown dynamics model %r" % (model,))
+    B, W = x_and_u.shape
+    out = torch.empty((B,) + _DYN_OUT[model], device=x_and_u.device, dtype=torch.float32)
+    if B == 0:
+        return out
+    with torch.cuda.device(x_and_u.device):
+        rc = lib.irbfn_integrate(model, _ptr(x_and_u), _dyn_array(dyn_params), _ptr(out), B, W, _stream())
+    _lib.check(rc, "irbfn_integrate")
+    return out
+
+
+# --------------------------------------------------------------------------- one-pass Jacobian
+def jacobian(x, centers, log_sigs, kernel, bias=None, *, gate=None, gd: GatePack = None,
+             basis: int = BASIS_GAUSSIAN, want_y: bool = False, want_region_y: bool = False):
+    """dy/dx (B,O,D) of the IRBFN forward in one launch per 4 output columns (irbfn_jacobian).
+    Returns jac, or (jac, y) / (jac, y, region_y) when asked."""
+    lib = _lib.load()
+    _chk(x, "x")
+    B, D = x.shape
+    _chk(centers, "centers")
+    R, K, Dc = centers.shape
+    if Dc != D:
+        raise ValueError("centers feature count %d != x feature count %d" % (Dc, D))
+    _chk(log_sigs, "log_sigs", (R, K))
+    _chk(kernel, "kernel")
+    O = kernel.shape[1]
+    _chk(kernel, "kernel", (K, O))
+    if want_y:
+        if bias is None:
+            raise ValueError("bias is required for y")
+        _chk(bias, "bias", (O,))
+    if gate is not None:
+        _chk(gate, "gate", (B, R))
+    jac = torch.empty((B, O, D), device=x.device, dtype=torch.float32)
+    y = torch.empty((B, O), device=x.device, dtype=torch.float32) if want_y else None
+    ry = torch.empty((B, R, O), device=x.device, dtype=torch.float32) if want_region_y else None
+    if want_region_y and gate is None and gd is not None and gd.num_ranges < R:
+        ry.zero_()          # regions without a range row have gamma == 0 and are skipped
+    if B > 0:
+        with torch.cuda.device(x.device):
+            rc = lib.irbfn_jacobian(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias) if want_y else None,
+                                    _ptr(gate), gd.ref() if gd is not None else None, _ptr(jac), _ptr(y),
+                                    _ptr(ry), B, R, K, D, O, basis, _stream())
+        _lib.check(rc, "irbfn_jacobian")
+    out = (jac,) + ((y,) if want_y else ()) + ((ry,) if want_region_y else ())
+    return out[0] if len(out) == 1 else out

@@ -4,9 +4,11 @@ one flat gradient buffer -> all-reduce -> clip_by_global_norm -> Adam.
 Mirrors the reference's step (scripts/train_nmpc.py:258-300: ``value_and_grad(loss_fn)`` then
 ``state.apply_gradients``; optimiser = ``optax.chain(clip_by_global_norm(g), adam(lr))`` at
 :231-233).  The reference's loss also rolls the prediction through the vehicle dynamics
-(dynamics.py); that term is a "next" row of SURVEY.md 8f and is not part of this step: the
-loss here is the prediction term alone, ``optax.l2_loss(y_pred, y).mean()`` or
-``|y_pred - y|.mean()`` (train_nmpc_frenet.py:402).
+(dynamics.py): ``loss="frenet_oneint" | "frenet_fullint" | "st_oneint" | "st_fullint"`` selects
+the reference's four loss_fn tails (train_nmpc_frenet.py:343-384, 399-413; train_nmpc.py:260-293,
+306-413), evaluated together with their cotangent by ONE fused launch (irbfn_dynamics_loss)
+instead of the reference's hstack + two vmapped lax.scan rollouts + their autodiff transposes.
+``loss="l2" | "l1"`` is the prediction term alone.
 
 Parameters, gradients and both Adam moments live in flat fp32 device buffers laid out
 [centers | log_sigs | kernel | bias]; the leaves of the params tree are views, so the whole
@@ -65,6 +67,8 @@ class TrainState:
         self.mask = (ops.GRAD_CENTERS if self.train_centers else 0) | \
                     (ops.GRAD_LOG_SIGS if self.train_log_sigs else 0) | ops.GRAD_KERNEL
         self.device = device
+        self.dyn_params = ops.default_dyn_params()   # scripts/train_nmpc_frenet.py:322-338
+        self.loss_terms = None
 
     @property
     def params(self) -> dict:
@@ -101,6 +105,9 @@ def loss_and_cotangent(y_pred: torch.Tensor, y: torch.Tensor, global_batch: int,
     raise ValueError("loss must be 'l2' or 'l1'")
 
 
+DYNAMICS_LOSSES = {"frenet_oneint": 0, "frenet_fullint": 1, "st_oneint": 2, "st_fullint": 3}
+
+
 def clip_and_adam_(state: TrainState):
     """optax.chain(clip_by_global_norm(max_norm), adam(lr)) on the flat buffers, in place."""
     g = state.grad
@@ -127,7 +134,12 @@ def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch:
     gd = m._gate_pack(dev)
     gb = int(global_batch) if global_batch is not None else int(x.shape[0])
     y_pred = ops.forward(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis)
-    lval, dy = loss_and_cotangent(y_pred, y, gb, loss)
+    if loss in DYNAMICS_LOSSES:
+        terms, dy = ops.dynamics_loss(DYNAMICS_LOSSES[loss], x, y_pred, y, state.dyn_params, gb)
+        state.loss_terms = terms          # [pred_loss, int_loss] of this shard (device)
+        lval = terms.sum()
+    else:
+        lval, dy = loss_and_cotangent(y_pred, y, gb, loss)
     ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gd=gd, basis=m._basis,
                  grad_mask=state.mask, flat_out=state.grad)
     if gb != x.shape[0]:

@@ -252,6 +252,19 @@ def wcrbf_vjp(x, params, cfg, dy, dtype=np.float64, chunk=512):
 # --------------------------------------------------------------------------
 # Flax msgpack checkpoint reader (flax.serialization format; ext type 1 = ndarray)
 # --------------------------------------------------------------------------
+def wcrbf_jacobian(x, params, cfg, dtype=np.float64, chunk=512):
+    """J[b,o,j] = d y[b,o] / d x[b,j]: jax.jacrev of WCRBFNet.__call__ (model.py:169-198), built
+    the way jacrev does it -- one VJP with a one-hot cotangent per output column."""
+    x = np.asarray(x, dtype=dtype)
+    O = np.asarray(params["linear"]["kernel"]).shape[1]
+    J = np.empty((x.shape[0], O, x.shape[1]), dtype=dtype)
+    for o in range(O):
+        dy = np.zeros((x.shape[0], O), dtype=dtype)
+        dy[:, o] = 1
+        J[:, o, :] = wcrbf_vjp(x, params, cfg, dy, dtype, chunk)["x"]
+    return J
+
+
 def load_flax_checkpoint(path):
     """Decode a Flax legacy msgpack checkpoint (saved at scripts/train_nmpc.py:497-502)
     with ``msgpack`` alone.  Returns the raw tree {step, params:{params:{...}}, opt_state}."""

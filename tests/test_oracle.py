@@ -53,6 +53,7 @@ def test_survey_spot_value():
     survey session by a separate torch restatement on float64 params (the fixture holds the
     float32-cast params, hence 1e-6)."""
     import os
+    import os
     from conftest import GOLDEN_DIR
     cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c1b_nmpc_4_regions.npz"))
     y = orc.wcrbf_forward(arr["x"][:1].astype(np.float64), params, cfg)
@@ -132,6 +133,7 @@ def test_oracle_matches_literal_restatement_and_autograd(basis):
 def test_gate_is_not_normalised_and_overlaps_sum_above_one():
     """F4: overlapping regions (nmpc_4_regions) make the gates sum to more than 1."""
     import os
+    import os
     from conftest import GOLDEN_DIR
     cfg, _, arr = load_golden(os.path.join(GOLDEN_DIR, "c1b_nmpc_4_regions.npz"))
     gam = orc.region_activation(arr["x"], cfg["num_regions"], cfg["lower_bounds"],
@@ -183,3 +185,18 @@ def test_unsupported_basis_raises():
     cfg, p, x = _random_case(2)
     with pytest.raises(ValueError):
         orc.rbf_activations(x, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], 7)
+
+
+def test_jacobian_oracle_matches_finite_differences():
+    """wcrbf_jacobian (jacrev by one-hot VJPs) against central differences of the float64 forward."""
+    import os
+    from conftest import GOLDEN_DIR
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    x = arr["x"][:16].astype(np.float64)
+    J = orc.wcrbf_jacobian(x, params, cfg)
+    h = 1e-6
+    for j in range(x.shape[1]):
+        e = np.zeros_like(x)
+        e[:, j] = h
+        fd = (orc.wcrbf_forward(x + e, params, cfg) - orc.wcrbf_forward(x - e, params, cfg)) / (2 * h)
+        assert np.abs(fd - J[:, :, j]).max() <= 1e-6 * max(1.0, np.abs(J).max())
