@@ -155,6 +155,16 @@ __global__ void __launch_bounds__(256) softmax_gate_kernel(const float* __restri
     for (int r = lane; r < R; r += 32) gate[q * R + r] *= inv;
 }
 
+// y[i] = sum_s part[s][i] in split order (deterministic) -- closes the small-batch split-K forward
+__global__ void __launch_bounds__(256) split_reduce_kernel(const float* __restrict__ part, float* __restrict__ y,
+                                                           int nsplit, long long n) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = part[i];
+    for (int k = 1; k < nsplit; ++k) s += part[(size_t)k * n + i];
+    y[i] = s;
+}
+
 }  // namespace irbfn
 
 using namespace irbfn;
@@ -181,12 +191,20 @@ const char* irbfn_error_string(int code) {
     }
 }
 
-size_t irbfn_forward_workspace_bytes(int64_t, int, int, int, int, int) { return 0; }
+size_t irbfn_forward_workspace_bytes(int64_t B, int R, int K, int D, int O, int fused_gate) {
+    (void)R; (void)D; (void)fused_gate;
+    if (B <= 0 || K <= 0 || O <= 0) return 0;
+    int sms = 148, smem = 0;
+    device_info(&sms, &smem);   // keeps the nominal B200 value when no device is present
+    int kps;
+    const int ns = fwd_split(B, K, sms, &kps);
+    return ns > 1 ? (size_t)ns * (size_t)B * (size_t)O * sizeof(float) : 0;
+}
 
 int irbfn_forward(const float* x, const float* centers, const float* log_sigs, const float* W,
                   const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
-                  float* hidden, int64_t B, int R, int K, int D, int O, int basis, void*, size_t,
-                  irbfn_stream_t stream) {
+                  float* hidden, int64_t B, int R, int K, int D, int O, int basis, void* workspace,
+                  size_t workspace_bytes, irbfn_stream_t stream) {
     if (B < 0 || R <= 0 || K <= 0 || D <= 0) return IRBFN_ERR_BAD_DIMS;
     if (y != nullptr && O <= 0) return IRBFN_ERR_BAD_DIMS;
     if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
@@ -210,13 +228,30 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
     const int Ototal = y ? O : 0;
     int o0 = 0;
     bool first = true;
+    // Small batches leave most SMs idle with one CTA per 1,024 queries: split the kernels of every
+    // region over gridDim.y, partial readouts into the workspace, fixed-order reduction afterwards.
+    // Without (enough) workspace the unsplit path runs -- same result, more latency.
+    int k_per_split = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
+    int nsplit = fwd_split(B, K, dev.sms, &k_per_split);
+    float* part = nullptr;
+    if (nsplit > 1 && y != nullptr) {
+        if (workspace != nullptr && workspace_bytes >= (size_t)nsplit * (size_t)B * (size_t)O * sizeof(float))
+            part = (float*)workspace;
+        else {
+            nsplit = 1;
+            k_per_split = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
+        }
+    }
     // Output windows of at most 16 columns; the hidden activations ride along the first one.
     do {
         const int ocur = Ototal - o0 > 16 ? 16 : Ototal - o0;
         const int OT = fwd_ot_for(ocur);
         FwdPlan plan;
-        if (!plan_forward(R, K, DT, OT, dev.smem_optin, &plan)) return IRBFN_ERR_BAD_DIMS;
+        if (!plan_forward(R, nsplit > 1 ? k_per_split : K, DT, OT, dev.smem_optin, &plan)) return IRBFN_ERR_BAD_DIMS;
         FwdArgs a{};
+        a.nsplit = nsplit;
+        a.k_per_split = k_per_split;
+        a.split_stride = part ? (long long)B * O : 0;
         a.x = x;
         a.centers = centers;
         a.log_sigs = log_sigs;
@@ -224,7 +259,7 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
         a.bias = bias;
         a.gate_ext = gate;
         a.gd = gdev;
-        a.y = ocur > 0 ? y : nullptr;
+        a.y = ocur > 0 ? (part ? part : y) : nullptr;
         a.hidden = first ? hidden : nullptr;
         a.B = B;
         a.R = R;
@@ -252,6 +287,12 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
         o0 += ocur;
         first = false;
     } while (o0 < Ototal);
+    if (part) {
+        const long long n = (long long)B * O;
+        split_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, y, nsplit, n);
+        const cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return note_cuda_error("split_reduce_kernel", (int)e);
+    }
     return IRBFN_OK;
 }
 

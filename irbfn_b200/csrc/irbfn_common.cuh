@@ -70,6 +70,11 @@ struct FwdArgs {
     int KC;                 // kernels per stage (multiple of the kernel tile)
     int num_tiles;          // ceil(B / queries-per-block)
     int stage_once;         // 1: a single (region, kernel) stage -> staged once per block
+    // small-batch split over kernels: blockIdx.y owns kernels [y * k_per_split, (y+1) * k_per_split) of
+    // every region and writes its partial readout to y + blockIdx.y * split_stride (bias from split 0)
+    int nsplit;             // gridDim.y
+    int k_per_split;        // multiple of the kernel tile; >= K when gridDim.y == 1
+    long long split_stride; // floats between partial outputs (0 when gridDim.y == 1)
 };
 
 // log-sigma -> the per-kernel scale used in the hot loop.

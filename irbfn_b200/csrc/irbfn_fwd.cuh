@@ -51,7 +51,11 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
     const int tid = threadIdx.x;
     const int R = a.R, K = a.K, RC = a.RC, KC = a.KC;
     const int n_rch = (R + RC - 1) / RC;
-    const int n_kch = (K + KC - 1) / KC;
+    const int kb = blockIdx.y * a.k_per_split;              // this CTA's kernel range (split-K for small batches)
+    const int ke = min(K, kb + a.k_per_split);
+    const int n_kch = (ke - kb + KC - 1) / KC;
+    float* const ybase = a.y != nullptr ? a.y + (size_t)blockIdx.y * a.split_stride : nullptr;
+    const bool add_bias = blockIdx.y == 0;
     bool staged = false;
 
     for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
@@ -75,8 +79,8 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
 #pragma unroll
             for (int op = 0; op < OP; ++op) {
                 float2 bv;
-                bv.x = (2 * op < a.ocur) ? __ldg(a.bias + a.o0 + 2 * op) : 0.f;
-                bv.y = (2 * op + 1 < a.ocur) ? __ldg(a.bias + a.o0 + 2 * op + 1) : 0.f;
+                bv.x = (add_bias && 2 * op < a.ocur) ? __ldg(a.bias + a.o0 + 2 * op) : 0.f;
+                bv.y = (add_bias && 2 * op + 1 < a.ocur) ? __ldg(a.bias + a.o0 + 2 * op + 1) : 0.f;
 #pragma unroll
                 for (int q = 0; q < Q; ++q) y2[q][op] = bv;
             }
@@ -129,8 +133,8 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
             }
 
             for (int kch = 0; kch < n_kch; ++kch) {
-                const int k0 = kch * KC;
-                const int kc = min(KC, K - k0);
+                const int k0 = kb + kch * KC;
+                const int kc = min(KC, ke - k0);
                 const int kcp = ((kc + KT - 1) / KT) * KT;
 
                 // ---- stage parameters of (region chunk, kernel chunk), transposed per 4-kernel tile ----
@@ -301,7 +305,7 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
             for (int q = 0; q < Q; ++q) {
                 const long long qq = q0 + q;
                 if (qq < a.B) {
-                    float* yp = a.y + qq * a.ldw + a.o0;
+                    float* yp = ybase + qq * a.ldw + a.o0;
 #pragma unroll
                     for (int op = 0; op < OP; ++op) {
                         if (2 * op < a.ocur) yp[2 * op] = y2[q][op].x;
@@ -319,7 +323,7 @@ inline int launch_fwd_inst(const FwdArgs& a, int grid, size_t smem, cudaStream_t
     auto kern = irbfn_fwd_kernel<D, OT, BASIS, NT>;
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    kern<<<grid, NT, smem, st>>>(a);
+    kern<<<dim3(grid, a.nsplit > 0 ? a.nsplit : 1), NT, smem, st>>>(a);
     return (int)cudaGetLastError();
 }
 

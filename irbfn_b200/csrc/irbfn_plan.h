@@ -27,6 +27,23 @@ inline int fwd_ot_for(int ocur) {
     return 16;
 }
 
+// Split of the kernels of every region over gridDim.y for batches too small to give every SM a query
+// tile.  Returns the number of splits (1 = none) and the kernels per split (multiple of kFwdKT).
+inline int fwd_split(long long B, int K, int sms, int* k_per_split) {
+    const int Kp = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
+    *k_per_split = Kp;
+    const long long tiles = (B + kFwdTQ - 1) / kFwdTQ;
+    if (tiles <= 0 || 2 * tiles > sms || Kp < 2 * kFwdKT) return 1;
+    const int want = (int)((sms + tiles - 1) / tiles);               // CTAs per query tile that fill the device
+    int kps = (Kp + want - 1) / want;
+    kps = ((kps + kFwdKT - 1) / kFwdKT) * kFwdKT;
+    if (kps < 2 * kFwdKT) kps = 2 * kFwdKT;                          // at least two kernel tiles per CTA
+    const int ns = (K + kps - 1) / kps;
+    if (ns <= 1) return 1;
+    *k_per_split = kps;
+    return ns;
+}
+
 struct FwdPlan {
     int RC;          // regions per stage
     int KC;          // kernels per stage (multiple of kFwdKT)

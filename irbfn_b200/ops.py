@@ -121,9 +121,11 @@ def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: Gate
     if B == 0:  # empty tensors have no storage to point at
         return (y, hidden) if want_y and want_hidden else (y if want_y else hidden)
     with torch.cuda.device(x.device):
+        nbytes = lib.irbfn_forward_workspace_bytes(B, R, K, D, O, 1 if gd is not None else 0)
+        ws = _workspace(nbytes, x.device)       # partial readouts of the small-batch split-K path
         rc = lib.irbfn_forward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias),
                                _ptr(gate), gd.ref() if gd is not None else None, _ptr(y),
-                               _ptr(hidden), B, R, K, D, O, basis, None, 0, _stream())
+                               _ptr(hidden), B, R, K, D, O, basis, _ptr(ws), nbytes, _stream())
     _lib.check(rc, "irbfn_forward")
     if want_y and want_hidden:
         return y, hidden

@@ -205,3 +205,36 @@ def test_forward_is_linear_in_the_readout(cuda_device):
     assert rel_max(y1[idx].cpu().numpy(), y_ref) < OUT_TOL
     # determinism: bit-identical across launches
     assert torch.equal(y1, ops.forward(x, c, ls, W1, b1, gd=gd))
+
+
+@pytest.mark.parametrize("B", [1, 400, 4096, 40000])
+def test_small_batch_split_over_kernels_matches_unsplit_and_oracle(B, cuda_device):
+    """Batches that cannot give every SM a query tile split the kernels over gridDim.y and reduce
+    the partial readouts in a fixed order (workspace-backed).  Same numbers as the unsplit launch
+    (which runs when no workspace is passed), both within tolerance of the oracle; hidden
+    activations come out right as well."""
+    import ctypes as C
+    from irbfn_b200 import _lib
+    ops = _ops()
+    cfg, p, x = _synthetic(41, B, 3, 250, 7, 10)
+    dev = cuda_device
+    gamma = orc.region_activation(x.astype(np.float64), 3, cfg["lower_bounds"], cfg["upper_bounds"],
+                                  cfg["delta"], cfg["dimension_ranges"])
+    y_ref, h_ref = orc.forward(x, p["centers"], p["log_sigs"], p["kernel"], p["bias"], gamma, 0, return_hidden=True)
+    xs, c, ls, W, b = (_t(a, dev) for a in (x, p["centers"], p["log_sigs"], p["kernel"], p["bias"]))
+    gd = _gd(cfg, dev)
+    lib = _lib.load()
+    need = lib.irbfn_forward_workspace_bytes(B, 3, 250, 7, 10, 1)
+    assert (need > 0) == (B <= 40000 and B * 2 <= 148 * 1024)
+    y, h = ops.forward(xs, c, ls, W, b, gd=gd, basis=0, want_hidden=True)
+    y0 = torch.empty_like(y)
+    rc = lib.irbfn_forward(C.c_void_p(xs.data_ptr()), C.c_void_p(c.data_ptr()), C.c_void_p(ls.data_ptr()),
+                           C.c_void_p(W.data_ptr()), C.c_void_p(b.data_ptr()), None, gd.ref(),
+                           C.c_void_p(y0.data_ptr()), None, B, 3, 250, 7, 10, 0, None, 0,
+                           C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    assert rel_max(y.cpu().numpy(), y_ref) < OUT_TOL
+    assert rel_max(y0.cpu().numpy(), y_ref) < OUT_TOL
+    assert rel_max(h.cpu().numpy(), h_ref) < OUT_TOL
+    y2 = ops.forward(xs, c, ls, W, b, gd=gd, basis=0)
+    assert torch.equal(y, y2)          # fixed-order reduction: bit-identical run to run
