@@ -355,6 +355,28 @@ def extras(net, params, cfg, dev, world, args):
     ms_l = timed(lambda: ops.dynamics_loss(1, xl, ypl, yl, state.dyn_params), args.steps, 3)
     res["dynamics_loss_fullint_8f1"] = {"samples": B4, "ms": ms_l, "hbm_GBps": B4 * 4 * (8 + 30) / (ms_l * 1e-3) / 1e9,
                                         "note": "five-step Frenet rollout x2 + adjoint, 152 B/sample"}
+    # 8f rank 3: on-device input pipeline -- one gather launch per step instead of a host gather + H2D copy
+    NT_ = 1 << 22
+    tabx, taby = torch.rand((NT_, 8), device=dev), torch.rand((NT_, 10), device=dev)
+    perm_ = torch.randperm(NT_, device=dev)[:GB]
+    gx, gy = torch.empty((GB, 8), device=dev), torch.empty((GB, 10), device=dev)
+    ms_ga = timed(lambda: ops.gather_rows(tabx, taby, perm_, x_out=gx, y_out=gy), args.steps, 3)
+    res["gather_rows_8f3"] = {"rows": GB, "table_rows": NT_, "ms": ms_ga,
+                              "hbm_GBps": GB * (2 * 72 + 8) / (ms_ga * 1e-3) / 1e9,
+                              "note": "per row: 8 B index + 72 B read + 72 B written"}
+    # 8f rank 4: the explicit side of the irbfn_vs_explicit sweep -- brute-force nearest table row
+    NTAB = 1 << 18
+    tab_ = (torch.rand((NTAB, D), device=dev) * torch.from_numpy(hi - lo).to(dev) + torch.from_numpy(lo).to(dev)).contiguous()
+    qn = x4[: 1 << 20].contiguous()
+    ms_nn = timed(lambda: ops.nearest_row(qn, tab_), 2, 1)
+    res["nearest_row_8f4"] = {"queries_per_gpu": 1 << 20, "table_rows": NTAB, "ms": ms_nn,
+                              "pairs_per_s": world * (1 << 20) * NTAB / (ms_nn * 1e-3),
+                              "lane_ops_T_per_s": (1 << 20) * NTAB * (2 * D) / (ms_nn * 1e-3) / 1e12,
+                              "timed_steps": 2, "warmup": 1}
+    q400 = x4[:400].contiguous()
+    ms_n4 = timed(lambda: ops.nearest_row(q400, tab_), 10, 3)
+    res["nearest_row_400_queries"] = {"queries": 400, "table_rows": NTAB, "ms": ms_n4}
+    del tabx, taby, tab_
     if not args.no_other:
         res.update(other_configs(dev, world, args, timed))
     return res

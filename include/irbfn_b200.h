@@ -246,6 +246,41 @@ int irbfn_jacobian(const float* x, const float* centers, const float* log_sigs, 
                    float* y, float* region_y, int64_t B, int R, int K, int D, int O, int basis,
                    irbfn_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Table-side kernels.
+ *
+ * irbfn_gather_rows: the training input pipeline on the device.  x_out[i,:] = X[index[i],:] and
+ * y_out[i,:] = Y[index[i],:] in one launch -- replaces the host-side NumPy gather + per-step
+ * host->device copy of scripts/train_nmpc_frenet.py:499-501 (batch_x = X[perm]).  X (N,D), Y (N,O)
+ * (Y / y_out may be NULL with O == 0), index (n) int64, all on the device.  An index outside [0,N)
+ * is never dereferenced: its output row is zero and *bad_index_flag (device int, caller-zeroed) is
+ * set to 1.  Bit-exact.
+ */
+int irbfn_gather_rows(const float* X, const float* Y, const int64_t* index, float* x_out, float* y_out,
+                      int64_t n, int64_t N, int D, int O, int* bad_index_flag, irbfn_stream_t stream);
+
+/*
+ * irbfn_grid_index: per dimension d, index[b,d] = min(len_d - 1, searchsorted(keys_d, q[b,d],
+ * side="right")) -- the grid lookup of ExplicitPlanner.plan (src/irbfn_mpc/explicit_planner.py:165-175).
+ * keys: all dimensions' sorted key arrays concatenated; offset (num_dims + 1) int32 prefix sums;
+ * q (B,num_dims); index (B,num_dims) int32.  Bit-exact with numpy.searchsorted (NaN sorts last).
+ */
+int irbfn_grid_index(const float* q, const float* keys, const int32_t* offset, int32_t* index,
+                     int64_t B, int num_dims, irbfn_stream_t stream);
+
+/*
+ * irbfn_nearest_row: index[b] = argmin_n || table[n,:] - q[b,:] ||_2 (first minimum wins), the
+ * brute-force lookup get_closest_ind (src/irbfn_mpc/explicit_planner.py:21-25) and
+ * irbfn_vs_explicit_frenet.ipynb cell 11, batched.  q (B,D), table (N,D), index (B) int64,
+ * distance (B) Euclidean distance of the winner or NULL.  Distances are accumulated in fp32
+ * (sequential FMA over the features); rows whose fp32 distances tie resolve to the lowest index.
+ * Small batches split the table across CTAs; the partial winners live in the workspace.
+ */
+size_t irbfn_nearest_row_workspace_bytes(int64_t B, int64_t N);
+
+int irbfn_nearest_row(const float* q, const float* table, int64_t* index, float* distance, int64_t B,
+                      int64_t N, int D, void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -34,6 +34,7 @@ EXPORTED_SYMBOLS = (
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_fp32_microbench", "irbfn_pipe_microbench", "irbfn_forward_plan",
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
+    "irbfn_gather_rows", "irbfn_grid_index", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
 )
 
 
@@ -101,6 +102,14 @@ def load():
     lib.irbfn_integrate.argtypes = [i, p, C.POINTER(C.c_float), p, i64, i, p]
     lib.irbfn_jacobian.restype = i
     lib.irbfn_jacobian.argtypes = [p, p, p, p, p, p, C.POINTER(GateDesc), p, p, p, i64, i, i, i, i, i, p]
+    lib.irbfn_gather_rows.restype = i
+    lib.irbfn_gather_rows.argtypes = [p, p, p, p, p, i64, i64, i, i, p, p]
+    lib.irbfn_grid_index.restype = i
+    lib.irbfn_grid_index.argtypes = [p, p, p, p, i64, i, p]
+    lib.irbfn_nearest_row_workspace_bytes.restype = sz
+    lib.irbfn_nearest_row_workspace_bytes.argtypes = [i64, i64]
+    lib.irbfn_nearest_row.restype = i
+    lib.irbfn_nearest_row.argtypes = [p, p, p, p, i64, i64, i, p, sz, p]
     if lib.irbfn_abi_version() != ABI_VERSION:
         raise ImportError("libirbfn_b200.so ABI %d != binding ABI %d"
                           % (lib.irbfn_abi_version(), ABI_VERSION))

@@ -19,6 +19,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
 __all__ = [
     "GatePack", "forward", "backward", "region_gate", "softmax_gate", "fp32_microbench", "pipe_microbench",
     "dynamics_loss", "integrate", "default_dyn_params", "jacobian",
+    "gather_rows", "GridKeys", "grid_index", "nearest_row",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
     "GRAD_X", "GRAD_GATE", "GRAD_PARAMS",
 ]
@@ -358,3 +359,86 @@ def jacobian(x, centers, log_sigs, kernel, bias=None, *, gate=None, gd: GatePack
         _lib.check(rc, "irbfn_jacobian")
     out = (jac,) + ((y,) if want_y else ()) + ((ry,) if want_region_y else ())
     return out[0] if len(out) == 1 else out
+
+
+# --------------------------------------------------------------------------- table-side kernels
+def gather_rows(X, Y, index, x_out=None, y_out=None, check: bool = False):
+    """(X[index], Y[index]) in one launch (irbfn_gather_rows); ``index`` is an int64 CUDA tensor.
+    ``check=True`` synchronises and raises IndexError if any index was outside [0, N)."""
+    lib = _lib.load()
+    _chk(X, "X")
+    N, D = X.shape
+    O = 0
+    if Y is not None:
+        _chk(Y, "Y")
+        if Y.shape[0] != N:
+            raise ValueError("X and Y must have the same number of rows")
+        O = Y.shape[1]
+    _chk(index, "index", dtype=torch.int64)
+    n = index.shape[0]
+    xb = x_out if x_out is not None else torch.empty((n, D), device=X.device, dtype=torch.float32)
+    yb = None
+    if Y is not None:
+        yb = y_out if y_out is not None else torch.empty((n, O), device=X.device, dtype=torch.float32)
+        _chk(yb, "y_out", (n, O))
+    _chk(xb, "x_out", (n, D))
+    flag = torch.zeros(1, device=X.device, dtype=torch.int32)
+    if n > 0:
+        with torch.cuda.device(X.device):
+            rc = lib.irbfn_gather_rows(_ptr(X), _ptr(Y), _ptr(index), _ptr(xb), _ptr(yb), n, N, D, O, _ptr(flag),
+                                       _stream())
+        _lib.check(rc, "irbfn_gather_rows")
+        if check and int(flag.item()) != 0:
+            raise IndexError("gather_rows: an index is outside [0, %d)" % N)
+    return (xb, yb) if Y is not None else xb
+
+
+class GridKeys:
+    """Sorted per-dimension key arrays of an explicit table (ExplicitPlanner.input_keys,
+    explicit_planner.py:165-175), packed flat on one device."""
+
+    def __init__(self, keys: Sequence[Sequence[float]], device):
+        self.device = torch.device(device)
+        self.lengths = [len(k) for k in keys]
+        if not keys or min(self.lengths) == 0:
+            raise ValueError("every dimension needs at least one key")
+        offs = np.concatenate([[0], np.cumsum(self.lengths)]).astype(np.int32)
+        self.keys = torch.tensor(np.concatenate([np.asarray(k, np.float32) for k in keys]), device=self.device)
+        self.offset = torch.tensor(offs, device=self.device)
+        self.num_dims = len(keys)
+
+
+def grid_index(q, gk: GridKeys):
+    """(B, num_dims) int32 grid indices: min(len_d - 1, searchsorted(keys_d, q[:, d], 'right'))."""
+    lib = _lib.load()
+    _chk(q, "q")
+    B, nd = q.shape
+    if nd != gk.num_dims:
+        raise ValueError("q has %d columns, the grid has %d dimensions" % (nd, gk.num_dims))
+    out = torch.empty((B, nd), device=q.device, dtype=torch.int32)
+    if B > 0:
+        with torch.cuda.device(q.device):
+            rc = lib.irbfn_grid_index(_ptr(q), _ptr(gk.keys), _ptr(gk.offset), _ptr(out), B, nd, _stream())
+        _lib.check(rc, "irbfn_grid_index")
+    return out
+
+
+def nearest_row(q, table, want_distance: bool = True):
+    """Brute-force nearest table row per query (irbfn_nearest_row): (index int64 (B,), distance (B,))."""
+    lib = _lib.load()
+    _chk(q, "q")
+    _chk(table, "table")
+    B, D = q.shape
+    N, Dt = table.shape
+    if Dt != D:
+        raise ValueError("table has %d columns, queries have %d" % (Dt, D))
+    idx = torch.empty(B, device=q.device, dtype=torch.int64)
+    dist = torch.empty(B, device=q.device, dtype=torch.float32) if want_distance else None
+    if B > 0:
+        with torch.cuda.device(q.device):
+            nbytes = lib.irbfn_nearest_row_workspace_bytes(B, N)
+            ws = _workspace(nbytes, q.device)
+            rc = lib.irbfn_nearest_row(_ptr(q), _ptr(table), _ptr(idx), _ptr(dist), B, N, D, _ptr(ws), nbytes,
+                                       _stream())
+        _lib.check(rc, "irbfn_nearest_row")
+    return (idx, dist) if want_distance else idx
