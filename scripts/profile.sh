@@ -16,4 +16,8 @@ ncu --set full --clock-control none --import-source on -k regex:irbfn_bwd_p_kern
     -o gpurun_out/prof_bwdp_${TAG} -f $CMD > gpurun_out/ncu_bwdp_${TAG}.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:irbfn_bwd_x_kernel -s 1 -c 1 \
     -o gpurun_out/prof_bwdx_${TAG} -f $CMD > gpurun_out/ncu_bwdx_${TAG}.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:irbfn_jac_kernel -s 1 -c 1 \
+    -o gpurun_out/prof_jac_${TAG} -f $CMD > gpurun_out/ncu_jac_${TAG}.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:nearest_row_kernel -s 1 -c 1 \
+    -o gpurun_out/prof_nearest_${TAG} -f $CMD > gpurun_out/ncu_nearest_${TAG}.log 2>&1
 ls -la gpurun_out/

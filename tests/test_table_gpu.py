@@ -80,9 +80,9 @@ def test_train_epoch_on_device_table_runs_and_lowers_the_loss(cuda_device):
     y = (arr["y64"] + 0.05).astype(np.float32)          # targets a constant offset away from the network
     tab = DeviceTable(x, y, cuda_device)
     state = TrainState(net, device_params({"params": params}, cuda_device), lr=1e-3, device=cuda_device)
-    first, _ = train_epoch(state, tab, 1024, 0, loss="frenet_fullint", rank=0, world=1)
+    first, _ = train_epoch(state, tab, 256, 0, loss="frenet_fullint", rank=0, world=1)
     for e in range(1, 6):
-        last, per_batch = train_epoch(state, tab, 1024, e, loss="frenet_fullint", rank=0, world=1)
+        last, per_batch = train_epoch(state, tab, 256, e, loss="frenet_fullint", rank=0, world=1)
     assert per_batch.shape == (4,)
     assert float(last) < float(first)
 
