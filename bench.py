@@ -126,9 +126,10 @@ def run_reference(args):
     cfg, p = load_c2()
     sample = 1 << 17
     x = lattice(cfg)[:: B_LATTICE // sample].copy()
-    cores = c_oracle.num_threads()
+    # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every core this process may run on
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     run = lambda: c_oracle.forward(x, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
-                                   p["linear"]["bias"], 0, cfg=cfg)
+                                   p["linear"]["bias"], 0, cfg=cfg, nthreads=cores)
     for _ in range(args.warmup):
         run()
     t0 = time.perf_counter()
@@ -263,9 +264,9 @@ def main():
             from oracle import c_oracle
             sample = 1 << 18
             xs_cpu = xs[0][:: B // sample].cpu().numpy().copy()
-            cores = c_oracle.num_threads()
+            cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
             run = lambda: c_oracle.forward(xs_cpu, p_np["rbf_list"]["centers"], p_np["rbf_list"]["log_sigs"],
-                                           p_np["linear"]["kernel"], p_np["linear"]["bias"], 0, cfg=cfg)
+                                           p_np["linear"]["kernel"], p_np["linear"]["bias"], 0, cfg=cfg, nthreads=cores)
             y_cpu = run()
             t0 = time.perf_counter()
             reps = 0
