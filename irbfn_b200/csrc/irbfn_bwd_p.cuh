@@ -13,9 +13,11 @@
 //     straight into their compute layout by cp.async (double buffered, one barrier per tile).  A
 //     query's scalars are broadcast operands of the packed instructions (SASS `Rn.F32`), so nothing
 //     is duplicated in shared memory.
-//   * dh_k = dy . W[k,:] is formed in the thread from its own readout rows when the output window
-//     is narrow (DHT = 1: O <= 4, the NMPC shapes); otherwise (wide O, or a dhidden cotangent) a
-//     per-tile table dh[q][k] is built once per tile and shared by all regions.
+//   * dh_k = dy . W[k,:] is formed in the thread from its own readout rows (DHT = 1) when the output
+//     is narrow (O <= 4, the NMPC shapes) or when the CTA's kernel chunk lies inside one region, so
+//     that nothing could share a table (K large: C2b, the C5 stress shape); otherwise (several
+//     regions over the same kernels, or a dhidden cotangent) a per-tile table dh[q][k] is built once
+//     per tile and shared by all regions of the chunk.
 //   * phi is recomputed from x and the parameters (nothing saved by the forward).
 //   * grid = splits x chunks: a chunk is a contiguous range of kernel pairs, a split a strided
 //     set of query tiles.  Every CTA writes its raw partial sums to the workspace once; a second
@@ -304,7 +306,7 @@ inline int launch_bwd_p_inst(const BwdPArgs& a, int grid, int nt, size_t smem, c
 
 template <int D, int OT>
 inline int launch_bwd_p_ot(const BwdPArgs& a, int basis, int dht, int grid, int nt, size_t smem, cudaStream_t st) {
-    constexpr int CAN_DHT = (OT == 2 || OT == 4) ? 1 : 0;
+    constexpr int CAN_DHT = OT > 0 ? 1 : 0;   // dh formed in-thread from the thread's own readout rows
     if (basis == IRBFN_BASIS_GAUSSIAN)
         return (dht && CAN_DHT) ? launch_bwd_p_inst<D, OT, IRBFN_BASIS_GAUSSIAN, CAN_DHT>(a, grid, nt, smem, st)
                                 : launch_bwd_p_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 0>(a, grid, nt, smem, st);

@@ -166,7 +166,11 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     int Rspan = (int)((flen + K - 1) / K) + 1;
     if (Rspan > R) Rspan = R;
     (void)Dsrc;
-    const int dht = (!has_dhid && O >= 1 && O <= 4 && (OT == 2 || OT == 4)) ? 1 : 0;
+    // in-thread dh: narrow outputs always; wide single-window outputs when the chunk's kernels belong to
+    // one region (a per-tile dh table would be used once, and costs 227 KB-limited tiles of ~80 queries)
+    const bool narrow = O >= 1 && O <= 4 && (OT == 2 || OT == 4);
+    const bool lone = O >= 1 && O <= 16 && OT >= O && flen < K;
+    const int dht = (!has_dhid && (narrow || lone)) ? 1 : 0;
     int TQ = 256;
     while (TQ >= 4 && bwdp_smem_floats(TQ, D, O, Kspan, Rspan, has_dhid, dht) * sizeof(float) > (size_t)smem_limit)
         TQ -= 4;
