@@ -130,13 +130,27 @@ __global__ void __launch_bounds__(kNearNT, 1) nearest_row_kernel(const NearestAr
                         }
                     }
                 }
-                const long long base = c0 + r;
+                // running (min, argmin): a min-tree over the tile's four rows and ONE rarely-taken branch per
+                // tile keep the compare/select chain off the ALU pipe (a query's minimum improves ~ln N times
+                // in N rows).  Rows are visited in increasing order and the update is a strict <, so fp32 ties
+                // keep the lowest index, like argmin.
+                float m[4];
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {                   // rows in increasing order, strict <:
-#pragma unroll                                                     // ties keep the lowest index (argmin)
+                for (int p = 0; p < 2; ++p) {
+                    m[2 * p] = fminf(fminf(acc[0][p].x, acc[1][p].x), fminf(acc[2][p].x, acc[3][p].x));
+                    m[2 * p + 1] = fminf(fminf(acc[0][p].y, acc[1][p].y), fminf(acc[2][p].y, acc[3][p].y));
+                }
+                if ((m[0] < best[0]) | (m[1] < best[1]) | (m[2] < best[2]) | (m[3] < best[3])) {
+                    const long long base = c0 + r;
+#pragma unroll
                     for (int p = 0; p < 2; ++p) {
-                        if (acc[kk][p].x < best[2 * p]) { best[2 * p] = acc[kk][p].x; bidx[2 * p] = base + kk; }
-                        if (acc[kk][p].y < best[2 * p + 1]) { best[2 * p + 1] = acc[kk][p].y; bidx[2 * p + 1] = base + kk; }
+#pragma unroll
+                        for (int kk = 3; kk >= 0; --kk) {          // descending: the first row that attains m wins
+                            if (acc[kk][p].x == m[2 * p] && m[2 * p] < best[2 * p]) bidx[2 * p] = base + kk;
+                            if (acc[kk][p].y == m[2 * p + 1] && m[2 * p + 1] < best[2 * p + 1]) bidx[2 * p + 1] = base + kk;
+                        }
+                        best[2 * p] = fminf(best[2 * p], m[2 * p]);
+                        best[2 * p + 1] = fminf(best[2 * p + 1], m[2 * p + 1]);
                     }
                 }
             }
