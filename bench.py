@@ -66,6 +66,16 @@ def lattice(cfg, vx_goal=4.0, curv=0.0, jitter=0.0):
     return x
 
 
+def _ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one forward launch from the committed ncu --set full
+    capture (profiles/traffic_fwd.json), or None."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic_fwd.json")))
+        return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
+    except Exception:
+        return None
+
+
 def algorithmic_counts(cfg):
     """Per-query algorithmic work."""
     R, K, D, O = cfg["num_regions"], cfg["num_kernels"], cfg["in_features"], cfg["out_features"]
@@ -244,7 +254,7 @@ def main():
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         out["roofline"] = {
             "bound": "fp32_pipe", "achieved": ach_lane / 1e12, "peak": peak_lane / 1e12, "unit": "T lane-op/s",
-            "frac": ach_lane / peak_lane, "traffic": None,
+            "frac": ach_lane / peak_lane, "traffic": _ncu_traffic(),
             "kernel": "irbfn_fwd_kernel<8,2,gaussian>", "launch_ms": ms,
             "note": "FP32-pipe lane-operations: R*K*(2D+2) + K*O per query (direct-form distance, scale, blend, "
                     "readout); peak = FADD2+FFMA2 micro-benchmark measured in this run",
