@@ -127,6 +127,29 @@ class ClockSampler(threading.Thread):
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Send everything libraries print on fd 1 (NCCL prints its version banner there when NCCL_DEBUG is set
+    on the box) to stderr, so that stdout carries exactly one line: the JSON result written by emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, line)
+
+
 def run_reference(args):
     """CPU arm: the C/OpenMP oracle port on all host cores, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
@@ -147,7 +170,7 @@ def run_reference(args):
         run()
     dt = (time.perf_counter() - t0) / args.steps
     v = sample / dt
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -157,7 +180,7 @@ def run_reference(args):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": "%d-point stride sample of the 2^20 lattice per step" % sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def main():
@@ -171,6 +194,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    quiet_stdout()
     if args.impl == "reference":
         return run_reference(args)
 
@@ -290,7 +314,7 @@ def main():
                                              "oracle/irbfn_oracle.c (float32, OpenMP)" % (sample, reps)}
             out["parity_check"] = {"max_abs_err_over_max_abs": float(np.abs(y_gpu - y_cpu).max() / np.abs(y_cpu).max()),
                                    "against": "C oracle float32, same %d queries" % sample}
-        print(json.dumps(out))
+        emit(out)
     elif not args.no_extras:
         extras(net, params, cfg, dev, world, args)   # collectives inside: every rank takes part
     if world > 1:
