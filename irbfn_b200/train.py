@@ -38,6 +38,7 @@ class TrainState:
         self.apply_fn = module.apply
         self.lr, self.max_grad_norm, self.b1, self.b2, self.eps = lr, max_grad_norm, b1, b2, eps
         self.step = 0
+        self.step_t = None            # device copy of the step count, used once the step is graph-captured
         R, K, D, O = module.num_regions, module.num_kernels, module.in_features, module.out_features
         rb = p.get("rbf_list", {})
         self.train_centers = "centers" in rb
@@ -50,7 +51,8 @@ class TrainState:
         shapes += [("kernel", (K, O)), ("bias", (O,))]
         n = sum(int(np.prod(s)) for _, s in shapes)
         self.flat = torch.empty(n, device=device, dtype=torch.float32)
-        self.grad = torch.zeros_like(self.flat)
+        self._grad_ext = torch.zeros(n + 1, device=device, dtype=torch.float32)   # [grad | loss]: ONE collective
+        self.grad = self._grad_ext[:n]
         self.mu = torch.zeros_like(self.flat)
         self.nu = torch.zeros_like(self.flat)
         self.views, self.gviews = {}, {}
@@ -117,8 +119,15 @@ def clip_and_adam_(state: TrainState):
     state.step += 1
     state.mu.mul_(state.b1).add_(g, alpha=1 - state.b1)
     state.nu.mul_(state.b2).addcmul_(g, g, value=1 - state.b2)
-    bc1 = 1 - state.b1 ** state.step
-    bc2 = 1 - state.b2 ** state.step
+    if state.step_t is None:
+        bc1 = 1 - state.b1 ** state.step
+        bc2 = 1 - state.b2 ** state.step
+    else:
+        # the step count lives on the device so that a captured CUDA graph of this update stays valid
+        # from replay to replay (GraphedTrainStep); float64 keeps b2 ** t exact enough for t ~ 1e6
+        state.step_t += 1
+        bc1 = (1 - torch.pow(torch.full_like(state.step_t, state.b1), state.step_t)).float()
+        bc2 = (1 - torch.pow(torch.full_like(state.step_t, state.b2), state.step_t)).float()
     state.flat.addcdiv_(state.mu / bc1, (state.nu / bc2).sqrt_().add_(state.eps), value=-state.lr)
     return gnorm
 
@@ -143,10 +152,9 @@ def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch:
     ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gd=gd, basis=m._basis,
                  grad_mask=state.mask, flat_out=state.grad)
     if gb != x.shape[0]:
-        buf = torch.cat([state.grad, lval.reshape(1)])   # loss rides along: still one collective
-        parallel.allreduce_sum_(buf)
-        state.grad.copy_(buf[:-1])
-        lval = buf[-1]
+        state._grad_ext[-1:].copy_(lval.reshape(1))      # loss rides along: still one collective, no concat
+        parallel.allreduce_sum_(state._grad_ext)
+        lval = state._grad_ext[-1].clone()
     return lval
 
 
@@ -158,3 +166,49 @@ def train_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch
     lval = grad_step(state, x, y, global_batch, loss)
     clip_and_adam_(state)
     return lval
+
+
+class GraphedTrainStep:
+    """One optimiser step captured in a CUDA graph and replayed (forward, fused loss, VJP, the NCCL
+    all-reduce, clip + Adam): at 8 GPUs the step holds ~0.1 ms of kernels, less than the host needs to
+    launch them one by one ("capture the step in a CUDA graph").
+
+    ``x`` / ``y`` are static device buffers of this rank's shard: fill them (``load`` or the on-device
+    gather of pipeline.DeviceTable writing straight into them) and call the object.  Capture warms the
+    step up on a side stream first; parameters and optimiser state are restored afterwards, so capturing
+    does not advance training."""
+
+    def __init__(self, state: TrainState, shard_rows: int, global_batch: Optional[int] = None, loss: str = "l2",
+                 warmup: int = 3):
+        m = state.module
+        dev = state.device
+        self.state, self.loss_name = state, loss
+        self.global_batch = int(global_batch) if global_batch is not None else int(shard_rows)
+        self.x = torch.zeros((shard_rows, m.in_features), device=dev)
+        self.y = torch.zeros((shard_rows, m.out_features), device=dev)
+        if state.step_t is None:
+            state.step_t = torch.full((), float(state.step), device=dev, dtype=torch.float64)
+        snap = (state.flat.clone(), state.mu.clone(), state.nu.clone(), state.step_t.clone(), state.step)
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):             # allocates workspaces, initialises NCCL channels
+                train_step(state, self.x, self.y, self.global_batch, loss)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = train_step(state, self.x, self.y, self.global_batch, loss)
+        torch.cuda.synchronize(dev)
+        state.flat.copy_(snap[0]); state.mu.copy_(snap[1]); state.nu.copy_(snap[2]); state.step_t.copy_(snap[3])
+        state.step = snap[4]
+
+    def load(self, x: torch.Tensor, y: torch.Tensor):
+        self.x.copy_(x, non_blocking=True)
+        self.y.copy_(y, non_blocking=True)
+        return self
+
+    def __call__(self):
+        self.graph.replay()
+        self.state.step += 1
+        return self.loss

@@ -187,3 +187,30 @@ def test_backward_errors(cuda_device):
     with pytest.raises(IrbfnError) as e:   # dgate only exists for an external gate
         ops.backward(*args, dy, gd=_gd(cfg, dev), grad_mask=ops.GRAD_GATE)
     assert e.value.code == -9
+
+
+def test_graph_captured_train_step_equals_eager_steps(cuda_device):
+    """GraphedTrainStep (forward, loss, VJP, clip + Adam in one CUDA graph) walks the same trajectory as
+    eager train_step calls, and capturing it does not advance the parameters."""
+    import os
+    from conftest import GOLDEN_DIR
+    from irbfn_b200.basis import gaussian
+    from irbfn_b200.model import WCRBFNet, device_params
+    from irbfn_b200.train import GraphedTrainStep, TrainState, train_step
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    mk = lambda: WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                          cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"],
+                          cfg["delta"])
+    x = torch.tensor(arr["x"][:3000], device=cuda_device)
+    y = torch.tensor((arr["y64"][:3000] + 0.1).astype(np.float32), device=cuda_device)
+    for loss in ("l2", "frenet_oneint"):
+        eager = TrainState(mk(), device_params({"params": params}, cuda_device), lr=1e-3, device=cuda_device)
+        graphed = TrainState(mk(), device_params({"params": params}, cuda_device), lr=1e-3, device=cuda_device)
+        step = GraphedTrainStep(graphed, 3000, loss=loss).load(x, y)
+        assert torch.equal(graphed.flat, eager.flat) and graphed.step == 0
+        for _ in range(4):
+            le = train_step(eager, x, y, loss=loss)
+            lg = step()
+            assert torch.allclose(le, lg, rtol=1e-6, atol=0)
+        assert graphed.step == 4
+        assert torch.allclose(graphed.flat, eager.flat, rtol=1e-5, atol=1e-7)
