@@ -13,19 +13,26 @@ import torch
 class HostPipeline:
     NBUF = 3
 
-    def __init__(self, device, in_features: int, out_features: int, chunk: int = 1 << 17):
+    def __init__(self, device, in_features: int, out_features: int, chunk: int = 1 << 17, copy_streams: int = 1):
         self.device = torch.device(device)
         self.D, self.O, self.chunk = in_features, out_features, int(chunk)
-        self.s_in = torch.cuda.Stream(self.device)
+        # Optionally cut each chunk's upload into `copy_streams` pieces on separate streams (separate DMA
+        # engines).  Measured on this pool (scripts/dev_h2d.py, dev_e2e.py): a lone 33.5 MB copy runs at
+        # 25-55 GB/s depending on the box and two concurrent copies reach 55 GB/s, but inside the pipeline
+        # the step is bound by the chunk kernels plus fill/drain, so 1 stream is the default.
+        self.ncopy = max(1, int(copy_streams))
+        self.s_ins = [torch.cuda.Stream(self.device) for _ in range(self.ncopy)]
+        self.s_in = self.s_ins[0]
         self.s_run = torch.cuda.Stream(self.device)
         self.s_out = torch.cuda.Stream(self.device)
         self.xd = [torch.empty((self.chunk, self.D), device=self.device) for _ in range(self.NBUF)]
         self.yd = [torch.empty((self.chunk, self.O), device=self.device) for _ in range(self.NBUF)]
-        self.ev_in = [torch.cuda.Event() for _ in range(self.NBUF)]
+        self.ev_in = [[torch.cuda.Event() for _ in range(self.ncopy)] for _ in range(self.NBUF)]
         self.ev_run = [torch.cuda.Event() for _ in range(self.NBUF)]
         self.ev_out = [torch.cuda.Event() for _ in range(self.NBUF)]
         self._pin_in = None
         self._pin_out = None
+        self._graphs, self._keep = {}, {}
 
     def _pinned_in(self, x):
         """x as a pinned fp32 CPU tensor (zero-copy when it already is one)."""
@@ -39,7 +46,7 @@ class HostPipeline:
         buf.copy_(t)
         return buf
 
-    def run(self, x, out, launch):
+    def run(self, x, out, launch, graph: bool = False, graph_key=()):
         """launch(x_dev_chunk, y_dev_chunk) enqueues the kernel on the current stream."""
         xin = self._pinned_in(x)
         B = xin.shape[0]
@@ -52,21 +59,56 @@ class HostPipeline:
             out = self._pin_out[:B]
         elif not (isinstance(out, torch.Tensor) and out.is_pinned() and tuple(out.shape) == (B, self.O)):
             raise ValueError("out must be a pinned CPU tensor of shape (B, %d)" % self.O)
+        if graph:
+            self._replay(xin, out, B, launch, graph_key)
+        else:
+            self._enqueue(xin, out, B, launch)
+        if ret_numpy:
+            torch.cuda.current_stream(self.device).synchronize()
+            return out.numpy().copy()
+        return out
+
+    def _replay(self, xin, out, B, launch, graph_key=()):
+        """The whole chunk pipeline (uploads, kernels, downloads, their cross-stream dependencies) captured
+        once per (input buffer, output buffer, batch) as a CUDA graph and replayed: one launch from the host
+        instead of ~20 stream operations per chunk, which otherwise bound the pipeline on the CPU."""
+        key = (xin.data_ptr(), out.data_ptr(), B) + tuple(graph_key)   # every pointer the graph bakes in
+        g = self._graphs.get(key)
+        if g is None:
+            self._enqueue(xin, out, B, launch)          # warm-up: workspaces, lazy kernel attributes
+            torch.cuda.current_stream(self.device).synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._enqueue(xin, out, B, launch)
+            if len(self._graphs) >= 8:
+                old = next(iter(self._graphs))
+                self._graphs.pop(old)
+                self._keep.pop(old, None)
+            self._graphs[key] = g
+            self._keep[key] = (xin, out)                # the captured host pointers must stay alive
+        g.replay()
+
+    def _enqueue(self, xin, out, B, launch):
         cur = torch.cuda.current_stream(self.device)
-        for s in (self.s_in, self.s_run, self.s_out):
+        for s in (*self.s_ins, self.s_run, self.s_out):
             s.wait_stream(cur)
         n = (B + self.chunk - 1) // self.chunk
         for i in range(n):
             b = i % self.NBUF
             lo, hi = i * self.chunk, min(B, (i + 1) * self.chunk)
             m = hi - lo
-            with torch.cuda.stream(self.s_in):
-                if i >= self.NBUF:
-                    self.s_in.wait_event(self.ev_run[b])      # kernel that read xd[b] is done
-                self.xd[b][:m].copy_(xin[lo:hi], non_blocking=True)
-                self.ev_in[b].record(self.s_in)
+            piece = (m + self.ncopy - 1) // self.ncopy
+            for k, s_in in enumerate(self.s_ins):
+                a, e = min(m, k * piece), min(m, (k + 1) * piece)
+                with torch.cuda.stream(s_in):
+                    if i >= self.NBUF:
+                        s_in.wait_event(self.ev_run[b])       # kernel that read xd[b] is done
+                    if e > a:
+                        self.xd[b][a:e].copy_(xin[lo + a:lo + e], non_blocking=True)
+                    self.ev_in[b][k].record(s_in)
             with torch.cuda.stream(self.s_run):
-                self.s_run.wait_event(self.ev_in[b])
+                for k in range(self.ncopy):
+                    self.s_run.wait_event(self.ev_in[b][k])
                 if i >= self.NBUF:
                     self.s_run.wait_event(self.ev_out[b])     # copy-out that read yd[b] is done
                 launch(self.xd[b][:m], self.yd[b][:m])
@@ -76,7 +118,3 @@ class HostPipeline:
                 out[lo:hi].copy_(self.yd[b][:m], non_blocking=True)
                 self.ev_out[b].record(self.s_out)
         cur.wait_stream(self.s_out)
-        if ret_numpy:
-            cur.synchronize()
-            return out.numpy().copy()
-        return out

@@ -29,5 +29,12 @@ def timed(fn, n=20, w=5):
 print("H2D 33.5MB ms", timed(lambda: xd.copy_(xh, non_blocking=True)))
 print("D2H 8.4MB ms", timed(lambda: yh.copy_(yd, non_blocking=True)))
 sms = torch.cuda.get_device_properties(dev).multi_processor_count
-for chunk in (1 << 15, 1 << 16, 1 << 17, sms * 512, sms * 1024, sms * 2048, 1 << 19, 1 << 20):
-    print("chunk", chunk, "e2e ms", timed(lambda: net.apply_host(params, xh, out=yh, chunk=chunk)))
+for graph in (False, True):
+    for ncopy in (1, 2):
+        for chunk in (sms * 1024, sms * 2048):
+            print("graph", graph, "copy streams", ncopy, "chunk", chunk, "e2e ms",
+                  timed(lambda: net.apply_host(params, xh, out=yh, chunk=chunk, copy_streams=ncopy, graph=graph)))
+ref = net.apply_host(params, xh, out=torch.empty((B, 2)).pin_memory(), graph=False).clone()
+torch.cuda.synchronize()
+got = net.apply_host(params, xh, out=yh, graph=True); torch.cuda.synchronize()
+print("graph == eager:", torch.equal(ref, got))

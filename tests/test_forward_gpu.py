@@ -238,3 +238,33 @@ def test_small_batch_split_over_kernels_matches_unsplit_and_oracle(B, cuda_devic
     assert rel_max(h.cpu().numpy(), h_ref) < OUT_TOL
     y2 = ops.forward(xs, c, ls, W, b, gd=gd, basis=0)
     assert torch.equal(y, y2)          # fixed-order reduction: bit-identical run to run
+
+
+def test_host_pipeline_variants_agree(cuda_device):
+    """apply_host: default pipeline, two upload streams, and the CUDA-graph replay of the whole chunk
+    pipeline (twice: capture, then replay with new input VALUES in the same pinned buffers) all give the
+    device-resident result."""
+    import os
+    from conftest import GOLDEN_DIR
+    from irbfn_b200.basis import gaussian
+    from irbfn_b200.model import WCRBFNet, device_params
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                   cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"],
+                   cfg["delta"])
+    dp = device_params({"params": params}, cuda_device)
+    x = np.tile(arr["x"], (5, 1))[:5000].astype(np.float32)
+    xh = torch.from_numpy(x.copy()).pin_memory()
+    yh = torch.empty((5000, 2)).pin_memory()
+    ref = net.apply(dp, torch.from_numpy(x).to(cuda_device)).cpu()
+    for kw in (dict(), dict(copy_streams=2), dict(graph=True), dict(graph=True)):
+        yh.zero_()
+        net.apply_host(dp, xh, out=yh, chunk=2048, **kw)
+        torch.cuda.synchronize()
+        assert torch.equal(yh, ref), kw
+    xh.mul_(0.5)                                      # new values, same buffers: the graph must pick them up
+    ref2 = net.apply(dp, xh.to(cuda_device)).cpu()
+    net.apply_host(dp, xh, out=yh, chunk=2048, graph=True)
+    torch.cuda.synchronize()
+    assert torch.equal(yh, ref2)
+    assert np.array_equal(net.apply_host(dp, x * 0.5, chunk=2048), ref2.numpy())
