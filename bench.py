@@ -415,6 +415,15 @@ def extras(net, params, cfg, dev, world, args):
     q400 = x4[:400].contiguous()
     ms_n4 = timed(lambda: ops.nearest_row(q400, tab_), 10, 3)
     res["nearest_row_400_queries"] = {"queries": 400, "table_rows": NTAB, "ms": ms_n4}
+    # the notebook's sweep end to end on the device: 20 x 20 lattice -> network, nearest row, row fetch, errors
+    from irbfn_b200.sweep import ExplicitTable, irbfn_vs_explicit, lattice_queries
+    etab = ExplicitTable(tab_.cpu().numpy(), np.random.default_rng(5).normal(size=(NTAB, O)).astype(np.float32), dev)
+    fixed = [0.0, 0.0, 1.076, 0.0, 4.0, 0.0, 0.0, 0.0][:D]
+    qlat = torch.from_numpy(lattice_queries({0: np.linspace(0, 2, 20), D - 2: np.linspace(0, 1, 20)}, fixed)).to(dev)
+    ms_sw = timed(lambda: irbfn_vs_explicit(net, params, etab, qlat, rank=0, world=1), 10, 3)
+    res["sweep_400_lattice_vs_explicit"] = {"queries": 400, "table_rows": NTAB, "ms": ms_sw,
+                                            "note": "irbfn_vs_explicit_frenet.ipynb cells 8-13 on one device"}
+    del etab
     del tabx, taby, tab_
     if not args.no_other:
         res.update(other_configs(dev, world, args, timed))

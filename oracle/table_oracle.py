@@ -56,3 +56,22 @@ def grid_index(q, keys):
         k = np.asarray(k, q.dtype)
         out[:, d] = np.minimum(len(k) - 1, np.searchsorted(k, q[:, d], side="right"))
     return out
+
+
+def lattice(axes, fixed):
+    """Cell 8 of scripts/irbfn_vs_explicit_frenet.ipynb: meshgrid(indexing="ij") over the chosen columns,
+    flattened, the other columns constant."""
+    cols = list(axes.keys())
+    mesh = np.meshgrid(*[np.asarray(axes[c], np.float64) for c in cols], indexing="ij")
+    n = mesh[0].size
+    x = np.empty((n, len(fixed)), np.float32)
+    x[:] = np.asarray(fixed, np.float32)
+    for c, g in zip(cols, mesh):
+        x[:, c] = g.flatten()
+    return x
+
+
+def explicit_lookup(queries, inputs, outputs, out_features):
+    """Cells 4, 11, 12: inds = argmin_row ||inputs - q||; outputs[inds].reshape((-1, O), order="F")."""
+    inds, d1, d2 = nearest_row(queries, inputs)
+    return inds, np.asarray(outputs)[inds].reshape((-1, out_features), order="F"), d1, d2
