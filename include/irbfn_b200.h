@@ -214,6 +214,22 @@ int irbfn_dynamics_loss(int mode, const float* x, const float* y_pred, const flo
                         irbfn_stream_t stream);
 
 /*
+ * The prediction term of the loss alone, any output width, with its cotangent, in one launch plus the
+ * deterministic reduction: replaces `optax.l2_loss(pred_u, u).mean()` (scripts/train_nmpc.py:287;
+ * IRBFN_PRED_LOSS_L2 = mean of 0.5 d^2) / `jnp.abs(pred_u - u).mean()` (scripts/train_nmpc_frenet.py:347)
+ * and their autodiff transposes.  y_pred, y, dy are (B,O) device arrays; loss is ONE device float, this
+ * shard's sum divided by global_batch * O.  Workspace: irbfn_prediction_loss_workspace_bytes(B, O).
+ */
+#define IRBFN_PRED_LOSS_L2 0
+#define IRBFN_PRED_LOSS_L1 1
+
+size_t irbfn_prediction_loss_workspace_bytes(int64_t B, int O);
+
+int irbfn_prediction_loss(int kind, const float* y_pred, const float* y, float* dy, float* loss,
+                          int64_t B, int O, int64_t global_batch, void* workspace, size_t workspace_bytes,
+                          irbfn_stream_t stream);
+
+/*
  * Plain rollouts (what irbfn_planner.py:212-214,510-518 and the losses call):
  *   IRBFN_DYN_FRENET_MULT         integrate_frenet_mult       dynamics.py:284-290  (B,18) -> (B,5,8)
  *   IRBFN_DYN_FRENET_ONESTEP_AUX  dynamic_frenet_onestep_aux  dynamics.py:293-383  (B,width>=8) -> (B,6)

@@ -35,6 +35,7 @@ EXPORTED_SYMBOLS = (
     "irbfn_softmax_gate", "irbfn_fp32_microbench", "irbfn_pipe_microbench", "irbfn_forward_plan",
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
     "irbfn_gather_rows", "irbfn_grid_index", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
+    "irbfn_prediction_loss_workspace_bytes", "irbfn_prediction_loss",
 )
 
 
@@ -96,6 +97,10 @@ def load():
     lib.irbfn_pipe_microbench.argtypes = [i, i, i, p, C.POINTER(C.c_double), C.POINTER(C.c_float), p]
     lib.irbfn_dynamics_loss_workspace_bytes.restype = sz
     lib.irbfn_dynamics_loss_workspace_bytes.argtypes = [i64]
+    lib.irbfn_prediction_loss_workspace_bytes.restype = sz
+    lib.irbfn_prediction_loss_workspace_bytes.argtypes = [i64, i]
+    lib.irbfn_prediction_loss.restype = i
+    lib.irbfn_prediction_loss.argtypes = [i, p, p, p, p, i64, i, i64, p, sz, p]
     lib.irbfn_dynamics_loss.restype = i
     lib.irbfn_dynamics_loss.argtypes = [i, p, p, p, C.POINTER(C.c_float), p, p, i64, i, i, i64, p, sz, p]
     lib.irbfn_integrate.restype = i

@@ -2,6 +2,7 @@
 // (how parameters are chunked through shared memory) and the two small gate kernels.
 // The heavy kernels live in irbfn_fwd.cuh / irbfn_bwd_x.cuh / irbfn_bwd_p.cuh and are
 // instantiated per feature count in their own translation units.
+#include <stdlib.h>
 #include <cuda_runtime.h>
 #include <stdio.h>
 
@@ -94,25 +95,8 @@ int check_gate(const float* gate, const IrbfnGateDesc* gd, int D, GateDev* out) 
 __global__ void __launch_bounds__(256) region_gate_kernel(const float* __restrict__ x, GateDev gd,
                                                           float* __restrict__ gamma, long long B,
                                                           int R, int D) {
-    extern __shared__ float fac[];  // [256][num_bounds] thread-private rows
-    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= B) return;
-    float* f = fac + (size_t)threadIdx.x * gd.num_bounds;
-    for (int j = 0; j < gd.S; ++j) {
-        const float xv = __ldg(x + q * D + j);
-        const float k2 = 2.0f * kLog2e * __ldg(gd.delta + j);
-        for (int i = __ldg(gd.offset + j); i < __ldg(gd.offset + j + 1); ++i)
-            f[i] = gate_sigmoid(k2, xv - __ldg(gd.lower + i)) * gate_sigmoid(k2, __ldg(gd.upper + i) - xv);
-    }
-    for (int r = 0; r < R; ++r) {
-        float g = 0.f;
-        if (r < gd.num_ranges) {
-            g = 1.f;
-            for (int j = 0; j < gd.S; ++j)
-                g *= f[__ldg(gd.offset + j) + __ldg(gd.ranges + r * gd.S + j)];
-        }
-        gamma[q * R + r] = g;
-    }
+    extern __shared__ float fac[];  // [num_bounds][256] thread-private columns + the region index table
+    gate_rows_block(x, gd, gamma, B, R, D, fac);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -192,12 +176,13 @@ const char* irbfn_error_string(int code) {
 }
 
 size_t irbfn_forward_workspace_bytes(int64_t B, int R, int K, int D, int O, int fused_gate) {
-    (void)R; (void)D; (void)fused_gate;
+    (void)D; (void)fused_gate;
     if (B <= 0 || K <= 0 || O <= 0) return 0;
     int sms = 148, smem = 0;
     device_info(&sms, &smem);   // keeps the nominal B200 value when no device is present
     int kps;
-    const int ns = fwd_split(B, K, sms, &kps);
+    int ns = fwd_split(B, R, K, sms, &kps);
+    if (const char* dv = getenv("IRBFN_DEV_KPS")) { kps = atoi(dv); ns = (K + kps - 1) / kps; }
     return ns > 1 ? (size_t)ns * (size_t)B * (size_t)O * sizeof(float) : 0;
 }
 
@@ -232,7 +217,8 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
     // region over gridDim.y, partial readouts into the workspace, fixed-order reduction afterwards.
     // Without (enough) workspace the unsplit path runs -- same result, more latency.
     int k_per_split = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
-    int nsplit = fwd_split(B, K, dev.sms, &k_per_split);
+    int nsplit = fwd_split(B, R, K, dev.sms, &k_per_split);
+    if (const char* dv = getenv("IRBFN_DEV_KPS")) { k_per_split = atoi(dv); nsplit = (K + k_per_split - 1) / k_per_split; }
     float* part = nullptr;
     if (nsplit > 1 && y != nullptr) {
         if (workspace != nullptr && workspace_bytes >= (size_t)nsplit * (size_t)B * (size_t)O * sizeof(float))
@@ -322,7 +308,7 @@ int irbfn_region_gate(const float* x, const IrbfnGateDesc* gd, float* gamma, int
     DevInfo dev;
     rc = query_device(&dev);
     if (rc != IRBFN_OK) return rc;
-    const size_t smem = (size_t)256 * gdev.num_bounds * sizeof(float);
+    const size_t smem = gate_rows_smem_bytes(gdev.num_bounds, 1, gdev.num_ranges, gdev.S);
     if (smem > (size_t)dev.smem_optin) return IRBFN_ERR_BAD_GATE;
     if (smem > 48 * 1024 &&
         cudaFuncSetAttribute(region_gate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

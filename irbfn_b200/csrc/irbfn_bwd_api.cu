@@ -44,53 +44,78 @@ struct ReduceArgs {
     int splits, db_blocks, R, K, D, Dsrc, PW, O, o0, ocur;
 };
 
-// One warp per output element: lane l sums terms l, l+32, ... in order, then a fixed xor-shuffle
-// tree combines the 32 lane sums.  The order depends only on the launch geometry: deterministic.
-__device__ __forceinline__ double warp_sum_fixed(double s) {
+// 32 consecutive output elements per block, one per lane, so that every read of a split's partial
+// sums is a coalesced row segment; the block's 32 warps take the terms t = w, w+32, ... in order, eight
+// independent loads in flight at a time (double accumulation), and warp 0 adds the 32 phase sums in
+// phase order.  The order depends only on the launch geometry: deterministic.  (The first version gave
+// each element to one warp with the splits over its lanes: every lane read a lone 4-byte word of a
+// different split, 8x the traffic, and the R * splits terms of a dW element were a chain of dependent
+// loads that set the kernel's time: 35 us at C3.)
+constexpr int kReducePhases = 32;
+template <typename PtrOf>
+__device__ __forceinline__ double phase_sum(unsigned terms, int w, PtrOf ptr_of) {   // 32-bit term index: a 64-bit
+    double s = 0.0;                                                                   // divide per term cost 25 us here
+    unsigned t = (unsigned)w;
+    for (; t + 7 * kReducePhases < terms; t += 8 * kReducePhases) {
+        float v[8];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        for (int i = 0; i < 8; ++i) v[i] = *ptr_of(t + i * kReducePhases);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += (double)v[i];
+    }
+    for (; t < terms; t += kReducePhases) s += (double)*ptr_of(t);
     return s;
 }
 
-__global__ void __launch_bounds__(256) reduce_p_kernel(const ReduceArgs a) {
+__global__ void __launch_bounds__(32 * kReducePhases) reduce_p_kernel(const ReduceArgs a) {
+    __shared__ double red[kReducePhases][32];
     const long long RK = (long long)a.R * a.K;
-    const long long nC = a.dC ? RK * a.Dsrc : 0;
-    const long long nL = a.dLS ? RK : 0;
+    const int DC = a.D + 1;                                       // dC columns (D, zero-padded) + the dLS column
+    const long long nCL = (a.dC || a.dLS) ? RK * DC : 0;
     const long long nW = a.dW ? (long long)a.K * a.ocur : 0;
     const long long nB = a.db ? a.O : 0;
-    const int lane = threadIdx.x & 31;
-    const long long e = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;   // warp-uniform
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const long long e = (long long)blockIdx.x * 32 + lane;
     const size_t sstride = (size_t)RK * a.PW;
-    if (e < nC) {
-        const long long f = e / a.Dsrc;
-        const int j = (int)(e - f * a.Dsrc);
-        double s = 0.0;
-        for (int sp = lane; sp < a.splits; sp += 32) s += (double)a.part[sp * sstride + (size_t)f * a.PW + j];
-        s = warp_sum_fixed(s);
-        if (lane == 0) a.dC[e] = (float)(2.0 * exp(-2.0 * (double)a.log_sigs[f]) * s);
-    } else if (e < nC + nL) {
-        const long long f = e - nC;
-        double s = 0.0;
-        for (int sp = lane; sp < a.splits; sp += 32) s += (double)a.part[sp * sstride + (size_t)f * a.PW + a.D];
-        s = warp_sum_fixed(s);
-        if (lane == 0) a.dLS[f] = (float)(2.0 * exp(-2.0 * (double)a.log_sigs[f]) * s);
-    } else if (e < nC + nL + nW) {
-        const long long i = e - nC - nL;
+    double s = 0.0;
+    if (e < nCL) {
+        const long long f = e / DC;
+        const int c = (int)(e - f * DC);
+        const float* p = a.part + (size_t)f * a.PW + c;
+        s = phase_sum((unsigned)a.splits, w, [&](unsigned t) { return p + (size_t)t * sstride; });
+    } else if (e < nCL + nW) {
+        const long long i = e - nCL;
         const int k = (int)(i / a.ocur), o = (int)(i - (long long)k * a.ocur);
-        double s = 0.0;
-        const long long terms = (long long)a.R * a.splits;
-        for (long long t = lane; t < terms; t += 32) {
-            const int r = (int)(t / a.splits), sp = (int)(t - (long long)r * a.splits);
-            s += (double)a.part[sp * sstride + ((size_t)r * a.K + k) * a.PW + a.D + 1 + o];
-        }
-        s = warp_sum_fixed(s);
-        if (lane == 0) a.dW[(size_t)k * a.O + a.o0 + o] = (float)s;
-    } else if (e < nC + nL + nW + nB) {
-        const int o = (int)(e - nC - nL - nW);
-        double s = 0.0;
-        for (int sp = lane; sp < a.db_blocks; sp += 32) s += (double)a.part_db[(size_t)sp * a.O + o];
-        s = warp_sum_fixed(s);
-        if (lane == 0) a.db[o] = (float)s;
+        const float* p = a.part + (size_t)k * a.PW + a.D + 1 + o;
+        const size_t rstride = (size_t)a.K * a.PW;
+        const unsigned splits = (unsigned)a.splits;
+        s = phase_sum((unsigned)a.R * splits, w, [&](unsigned t) {        // R * splits < 2^31: checked by the host
+            const unsigned r = t / splits, sp = t - r * splits;
+            return p + (size_t)sp * sstride + (size_t)r * rstride;
+        });
+    } else if (e < nCL + nW + nB) {
+        const float* p = a.part_db + (int)(e - nCL - nW);
+        const int O = a.O;
+        s = phase_sum((unsigned)a.db_blocks, w, [&](unsigned t) { return p + (size_t)t * O; });
+    }
+    red[w][lane] = s;
+    __syncthreads();
+    if (w != 0) return;
+    s = red[0][lane];
+#pragma unroll
+    for (int ph = 1; ph < kReducePhases; ++ph) s += red[ph][lane];
+    if (e < nCL) {
+        const long long f = e / DC;
+        const int c = (int)(e - f * DC);
+        const double sc = 2.0 * exp(-2.0 * (double)a.log_sigs[f]);
+        if (c < a.Dsrc) { if (a.dC) a.dC[f * a.Dsrc + c] = (float)(sc * s); }
+        else if (c == a.D) { if (a.dLS) a.dLS[f] = (float)(sc * s); }
+    } else if (e < nCL + nW) {
+        const long long i = e - nCL;
+        const int k = (int)(i / a.ocur), o = (int)(i - (long long)k * a.ocur);
+        a.dW[(size_t)k * a.O + a.o0 + o] = (float)s;
+    } else if (e < nCL + nW + nB) {
+        a.db[(int)(e - nCL - nW)] = (float)s;
     }
 }
 
@@ -126,23 +151,7 @@ __global__ void __launch_bounds__(256) db_partial_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) gate_fill_kernel(const float* __restrict__ x, GateDev gd,
                                                         float* __restrict__ gamma, long long B, int R, int D) {
     extern __shared__ float fac[];
-    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= B) return;
-    float* f = fac + (size_t)threadIdx.x * gd.num_bounds;
-    for (int j = 0; j < gd.S; ++j) {
-        const float xv = __ldg(x + q * D + j);
-        const float k2 = 2.0f * kLog2e * __ldg(gd.delta + j);
-        for (int i = __ldg(gd.offset + j); i < __ldg(gd.offset + j + 1); ++i)
-            f[i] = gate_sigmoid(k2, xv - __ldg(gd.lower + i)) * gate_sigmoid(k2, __ldg(gd.upper + i) - xv);
-    }
-    for (int r = 0; r < R; ++r) {
-        float g = 0.f;
-        if (r < gd.num_ranges) {
-            g = 1.f;
-            for (int j = 0; j < gd.S; ++j) g *= f[__ldg(gd.offset + j) + __ldg(gd.ranges + r * gd.S + j)];
-        }
-        gamma[q * R + r] = g;
-    }
+    gate_rows_block(x, gd, gamma, B, R, D, fac);
 }
 
 // dx[q, j] += sum_r dgamma[q,r] * d gamma_r / d x_j      (tanh gate, model.py:70-95)
@@ -150,35 +159,41 @@ __global__ void __launch_bounds__(256) gate_fill_kernel(const float* __restrict_
 __global__ void __launch_bounds__(256) gate_bwd_kernel(const float* __restrict__ x, GateDev gd,
                                                        const float* __restrict__ dgamma,
                                                        float* __restrict__ dx, long long B, int R, int D) {
-    extern __shared__ float fac[];  // [256][2*num_bounds]
-    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= B) return;
-    float* f = fac + (size_t)threadIdx.x * 2 * gd.num_bounds;
-    float* fp = f + gd.num_bounds;
-    for (int j = 0; j < gd.S; ++j) {
-        const float xv = __ldg(x + q * D + j);
-        const float dl = __ldg(gd.delta + j);
-        const float k2 = 2.0f * kLog2e * dl;
-        for (int i = __ldg(gd.offset + j); i < __ldg(gd.offset + j + 1); ++i) {
-            const float sl = gate_sigmoid(k2, xv - __ldg(gd.lower + i));
-            const float su = gate_sigmoid(k2, __ldg(gd.upper + i) - xv);
-            f[i] = sl * su;
-            fp[i] = 2.0f * dl * sl * su * (su - sl);
+    extern __shared__ float fac[];  // factor columns f[i][256], derivative columns fp[i][256], region index table
+    const int tid = threadIdx.x;
+    const long long q = (long long)blockIdx.x * blockDim.x + tid;
+    const int nb = gd.num_bounds;
+    float* f = fac;
+    float* fp = fac + (size_t)256 * nb;
+    const int rmax = R < gd.num_ranges ? R : gd.num_ranges;
+    const int* ridx = gate_index_table(gd, fac + (size_t)512 * nb, rmax);
+    if (q < B) {
+        for (int j = 0; j < gd.S; ++j) {
+            const float xv = __ldg(x + q * D + j);
+            const float dl = __ldg(gd.delta + j);
+            const float k2 = 2.0f * kLog2e * dl;
+            for (int i = __ldg(gd.offset + j); i < __ldg(gd.offset + j + 1); ++i) {
+                const float sl = gate_sigmoid(k2, xv - __ldg(gd.lower + i));
+                const float su = gate_sigmoid(k2, __ldg(gd.upper + i) - xv);
+                f[i * 256 + tid] = sl * su;
+                fp[i * 256 + tid] = 2.0f * dl * sl * su * (su - sl);
+            }
         }
     }
+    __syncthreads();
+    if (q >= B) return;
     float acc[IRBFN_MAX_S];
 #pragma unroll
     for (int j = 0; j < IRBFN_MAX_S; ++j) acc[j] = 0.f;
-    const int rmax = R < gd.num_ranges ? R : gd.num_ranges;
     for (int r = 0; r < rmax; ++r) {
         const float dg = __ldg(dgamma + q * R + r);
         float fv[IRBFN_MAX_S], fd[IRBFN_MAX_S];
 #pragma unroll
         for (int j = 0; j < IRBFN_MAX_S; ++j) {
             if (j < gd.S) {
-                const int i = __ldg(gd.offset + j) + __ldg(gd.ranges + r * gd.S + j);
-                fv[j] = f[i];
-                fd[j] = fp[i];
+                const int i = ridx[r * gd.S + j];
+                fv[j] = f[i * 256 + tid];
+                fd[j] = fp[i * 256 + tid];
             } else {
                 fv[j] = 1.f;
                 fd[j] = 0.f;
@@ -319,7 +334,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
         const float* gate_p = gate;
         if (gd != nullptr) {
             float* gbuf = (float*)(ws + L.gate_off);
-            const size_t gsm = (size_t)256 * gdev.num_bounds * sizeof(float);
+            const size_t gsm = gate_rows_smem_bytes(gdev.num_bounds, 1, gdev.num_ranges, gdev.S);
             if (gsm > (size_t)smem) return IRBFN_ERR_BAD_GATE;
             if (gsm > 48 * 1024 &&
                 cudaFuncSetAttribute(gate_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm) != cudaSuccess)
@@ -336,6 +351,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             BwdPPlan pp;
             if (!plan_bwd_p(B, R, K, DT, D, Oeff, OT, dhidden != nullptr, sms, smem, &pp)) return IRBFN_ERR_BAD_DIMS;
             if (pp.part_floats > L.max_part_floats) return IRBFN_ERR_WORKSPACE;
+            if ((long long)R * pp.splits >= (1ll << 31)) return IRBFN_ERR_BAD_DIMS;   // reduce_p_kernel's term index
             BwdPArgs a{};
             a.x = x; a.centers = centers; a.log_sigs = log_sigs; a.W = W; a.gate = gate_p;
             a.dy = dy; a.dhidden = dhidden;
@@ -362,14 +378,14 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             r.db = (first && (grad_mask & IRBFN_GRAD_KERNEL) && Oeff > 0) ? dbias : nullptr;
             r.splits = pp.splits; r.db_blocks = kDbBlocks; r.R = R; r.K = K; r.D = DT; r.Dsrc = D; r.PW = pp.PW;
             r.O = Oeff; r.o0 = o0; r.ocur = ocur;
-            const long long n = (r.dC ? (long long)R * K * D : 0) + (r.dLS ? (long long)R * K : 0) +
+            const long long n = ((r.dC || r.dLS) ? (long long)R * K * (DT + 1) : 0) +
                                 (r.dW ? (long long)K * ocur : 0) + (r.db ? Oeff : 0);
             if (r.db != nullptr) {
                 db_partial_kernel<<<kDbBlocks, 256, 0, st>>>(dy, (float*)(ws + L.partdb_off), B, Oeff);
                 { const cudaError_t ce = cudaGetLastError(); if (ce != cudaSuccess) return note_cuda_error("db_partial_kernel", (int)ce); }
             }
             if (n > 0) {
-                reduce_p_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(r);   // one warp per element
+                reduce_p_kernel<<<(unsigned)((n + 31) / 32), 32 * kReducePhases, 0, st>>>(r);   // 32 elements per block
                 { const cudaError_t ce = cudaGetLastError(); if (ce != cudaSuccess) return note_cuda_error("reduce_p_kernel", (int)ce); }
             }
             o0 += ocur;
@@ -420,7 +436,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
         }
         if (e != 0) return note_cuda_error("irbfn_bwd_x_kernel", e);
         if (gd != nullptr && (grad_mask & IRBFN_GRAD_X) && !fuse) {
-            const size_t gsm = (size_t)256 * 2 * gdev.num_bounds * sizeof(float);
+            const size_t gsm = gate_rows_smem_bytes(gdev.num_bounds, 2, gdev.num_ranges, gdev.S);
             if (gsm > (size_t)smem) return IRBFN_ERR_BAD_GATE;
             if (gsm > 48 * 1024 &&
                 cudaFuncSetAttribute(gate_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm) != cudaSuccess)

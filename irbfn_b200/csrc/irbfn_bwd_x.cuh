@@ -71,15 +71,7 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
         const long long q0 = (long long)tile * TQ + (long long)tid * Q;
 
         float2 x2[2][D];
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-            const long long qa = q0 + 2 * p, qb = qa + 1;
-#pragma unroll
-            for (int j = 0; j < D; ++j) {
-                x2[p][j].x = (qa < a.B && j < a.Dsrc) ? __ldg(a.x + qa * a.Dsrc + j) : 0.f;
-                x2[p][j].y = (qb < a.B && j < a.Dsrc) ? __ldg(a.x + qb * a.Dsrc + j) : 0.f;
-            }
-        }
+        load_queries4<D>(a.x, q0, a.B, a.Dsrc, x2);
         // cotangent rows, packed over the query pair
         float2 dy2[2][OTS];
         if (OT > 0) {
@@ -122,34 +114,7 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                     gcol[rr * NT] = g;
                 }
             } else {
-                const int S = a.gd.S;
-                for (int rr = 0; rr < rc; ++rr) {
-                    const float one = (r0 + rr < a.gd.num_ranges) ? 1.f : 0.f;
-                    gcol[rr * NT] = make_float4(one, one, one, one);
-                }
-                const int rlim = min(rc, a.gd.num_ranges - r0);
-#pragma unroll
-                for (int j = 0; j < D; ++j) {
-                    if (j < S) {
-                        const float k2 = 2.0f * kLog2e * __ldg(a.gd.delta + j);
-                        const int ob = __ldg(a.gd.offset + j), oe = __ldg(a.gd.offset + j + 1);
-                        for (int i = ob; i < oe; ++i) {
-                            const float lb = __ldg(a.gd.lower + i), ub = __ldg(a.gd.upper + i);
-                            float4 f;
-                            f.x = gate_sigmoid(k2, x2[0][j].x - lb) * gate_sigmoid(k2, ub - x2[0][j].x);
-                            f.y = gate_sigmoid(k2, x2[0][j].y - lb) * gate_sigmoid(k2, ub - x2[0][j].y);
-                            f.z = gate_sigmoid(k2, x2[1][j].x - lb) * gate_sigmoid(k2, ub - x2[1][j].x);
-                            f.w = gate_sigmoid(k2, x2[1][j].y - lb) * gate_sigmoid(k2, ub - x2[1][j].y);
-                            for (int rr = 0; rr < rlim; ++rr) {
-                                if (__ldg(a.gd.ranges + (r0 + rr) * S + j) == i - ob) {
-                                    float4 g = gcol[rr * NT];
-                                    g.x *= f.x; g.y *= f.y; g.z *= f.z; g.w *= f.w;
-                                    gcol[rr * NT] = g;
-                                }
-                            }
-                        }
-                    }
-                }
+                gate_columns(a.gd, a.x, q0, a.B, a.Dsrc, r0, rc, gcol, NT);
             }
             if (want_dg)
                 for (int rr = 0; rr < rc; ++rr) dgcol[rr * NT] = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -50,6 +50,139 @@ struct GateDev {
     const int* ranges;
 };
 
+// A thread's four consecutive query rows -> two packed pairs x2[p][j] = (x[q0+2p][j], x[q0+2p+1][j]).
+// Scalar loads on purpose: each lands directly in its half of an aligned register pair.  (LDG.128 over the
+// 16*D contiguous bytes was tried: the four-register destinations put the two halves of a pair in different
+// quads, and ptxas then re-forms the pairs with ~115 MOVs INSIDE the hot loop, 176 -> 292 instructions.)
+template <int D>
+__device__ __forceinline__ void load_queries4(const float* __restrict__ x, long long q0, long long B, int Dsrc,
+                                              float2 (&x2)[2][D]) {
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const long long qa = q0 + 2 * p, qb = qa + 1;
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+            x2[p][j].x = (qa < B && j < Dsrc) ? __ldg(x + qa * Dsrc + j) : 0.f;
+            x2[p][j].y = (qb < B && j < Dsrc) ? __ldg(x + qb * Dsrc + j) : 0.f;
+        }
+    }
+}
+
+// Region gate of a thread's four queries q0..q0+3 for regions [r0, r0 + rc), written to the thread-private
+// shared-memory column gcol[rr * stride]  (model.py:70-95: gamma_r = prod_j f_j[ranges[r][j]],
+// f_j[i] = s(x_j - lb_i) s(ub_i - x_j)).
+//   * Split dimensions with ONE interval give the same factor to every region: they are multiplied in
+//     registers first and the table starts from that product; only dimensions with several intervals touch
+//     the table, four intervals' factors at a time held in registers and selected per region by its
+//     (warp-uniform) interval index.  For the shipped 12-region Frenet gate (8 split dimensions, 12
+//     intervals, 3 dimensions with more than one) that is 36 table updates instead of 144.
+//   * Every loop is a RUNTIME loop and x_j is re-read from global memory (an L1 hit: the tile's rows were
+//     just loaded) instead of indexing the register copy, which would force the dimension loop to unroll
+//     into ~4,000 straight-line instructions executed once per tile (instruction-fetch stalls in ncu).
+//     Measured cost of the fused gate at C2: ~5 us of a 125 us tile (scripts/dev_gate_cost.py).
+__device__ __forceinline__ void gate_columns(const GateDev& gd, const float* __restrict__ x, long long q0,
+                                             long long B, int Dsrc, int r0, int rc, float4* gcol, int stride) {
+    const int S = gd.S;
+    const int rlim = min(rc, gd.num_ranges - r0);
+    auto load4 = [&](int j) {
+        float4 v;
+        v.x = q0 + 0 < B ? __ldg(x + (q0 + 0) * Dsrc + j) : 0.f;
+        v.y = q0 + 1 < B ? __ldg(x + (q0 + 1) * Dsrc + j) : 0.f;
+        v.z = q0 + 2 < B ? __ldg(x + (q0 + 2) * Dsrc + j) : 0.f;
+        v.w = q0 + 3 < B ? __ldg(x + (q0 + 3) * Dsrc + j) : 0.f;
+        return v;
+    };
+    auto factor = [&](const float4& v, float k2, int i) {
+        const float lb = __ldg(gd.lower + i), ub = __ldg(gd.upper + i);
+        float4 f;
+        f.x = gate_sigmoid(k2, v.x - lb) * gate_sigmoid(k2, ub - v.x);
+        f.y = gate_sigmoid(k2, v.y - lb) * gate_sigmoid(k2, ub - v.y);
+        f.z = gate_sigmoid(k2, v.z - lb) * gate_sigmoid(k2, ub - v.z);
+        f.w = gate_sigmoid(k2, v.w - lb) * gate_sigmoid(k2, ub - v.w);
+        return f;
+    };
+    float4 com = make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll 1
+    for (int j = 0; j < S; ++j) {
+        const int ob = __ldg(gd.offset + j), oe = __ldg(gd.offset + j + 1);
+        if (oe - ob == 1) {
+            const float4 f = factor(load4(j), 2.0f * kLog2e * __ldg(gd.delta + j), ob);
+            com.x *= f.x; com.y *= f.y; com.z *= f.z; com.w *= f.w;
+        }
+    }
+#pragma unroll 1
+    for (int rr = 0; rr < rc; ++rr) gcol[rr * stride] = rr < rlim ? com : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int j = 0; j < S; ++j) {
+        const int ob = __ldg(gd.offset + j), oe = __ldg(gd.offset + j + 1);
+        if (oe - ob > 1) {
+            const float k2 = 2.0f * kLog2e * __ldg(gd.delta + j);
+            const float4 v = load4(j);
+            const int* rg = gd.ranges + (size_t)r0 * S + j;
+#pragma unroll 1
+            for (int ib = ob; ib < oe; ib += 4) {
+                const float4 f0 = factor(v, k2, ib);
+                const float4 f1 = ib + 1 < oe ? factor(v, k2, ib + 1) : f0;
+                const float4 f2 = ib + 2 < oe ? factor(v, k2, ib + 2) : f0;
+                const float4 f3 = ib + 3 < oe ? factor(v, k2, ib + 3) : f0;
+#pragma unroll 2
+                for (int rr = 0; rr < rlim; ++rr) {
+                    const int idx = __ldg(rg + rr * S) - (ib - ob);
+                    if ((unsigned)idx < 4u) {
+                        const float4 lo = idx & 1 ? f1 : f0, hi = idx & 1 ? f3 : f2;
+                        const float4 f = idx & 2 ? hi : lo;
+                        float4 g = gcol[rr * stride];
+                        g.x *= f.x; g.y *= f.y; g.z *= f.z; g.w *= f.w;
+                        gcol[rr * stride] = g;
+                    }
+                }
+            }
+        }
+    }
+}
+
+// One thread per query, 256 per block: gamma (B,R) rows of the tanh gate.  Interval factors live in
+// thread-private shared-memory COLUMNS fac[i * 256 + tid] (conflict-free) and the per-region factor
+// indices offset[j] + ranges[r][j] in a block-shared table, built once per block instead of two dependent
+// global loads per (query, region, dimension).  Dynamic shared memory: gate_rows_smem_bytes().
+inline size_t gate_rows_smem_bytes(int num_bounds, int rows_per_bound, int num_ranges, int S) {
+    return ((size_t)256 * num_bounds * rows_per_bound + (size_t)num_ranges * S) * sizeof(float);
+}
+__device__ __forceinline__ int* gate_index_table(const GateDev& gd, float* smem_after_factors, int rmax) {
+    int* ridx = reinterpret_cast<int*>(smem_after_factors);
+    for (int t = threadIdx.x; t < rmax * gd.S; t += blockDim.x) {
+        const int r = t / gd.S, j = t - r * gd.S;
+        ridx[t] = __ldg(gd.offset + j) + __ldg(gd.ranges + r * gd.S + j);
+    }
+    return ridx;
+}
+__device__ __forceinline__ void gate_rows_block(const float* __restrict__ x, const GateDev& gd,
+                                                float* __restrict__ gamma, long long B, int R, int D,
+                                                float* fac) {
+    const int tid = threadIdx.x;
+    const long long q = (long long)blockIdx.x * blockDim.x + tid;
+    const int rmax = R < gd.num_ranges ? R : gd.num_ranges;
+    const int* ridx = gate_index_table(gd, fac + (size_t)256 * gd.num_bounds, rmax);
+    if (q < B) {
+        for (int j = 0; j < gd.S; ++j) {
+            const float xv = __ldg(x + q * D + j);
+            const float k2 = 2.0f * kLog2e * __ldg(gd.delta + j);
+            for (int i = __ldg(gd.offset + j); i < __ldg(gd.offset + j + 1); ++i)
+                fac[i * 256 + tid] = gate_sigmoid(k2, xv - __ldg(gd.lower + i)) * gate_sigmoid(k2, __ldg(gd.upper + i) - xv);
+        }
+    }
+    __syncthreads();
+    if (q >= B) return;
+    for (int r = 0; r < R; ++r) {
+        float g = 0.f;
+        if (r < rmax) {
+            g = 1.f;
+            for (int j = 0; j < gd.S; ++j) g *= fac[ridx[r * gd.S + j] * 256 + tid];
+        }
+        gamma[q * R + r] = g;
+    }
+}
+
 // Forward launch arguments (one struct, passed by value).
 struct FwdArgs {
     const float* x;         // (B,D)

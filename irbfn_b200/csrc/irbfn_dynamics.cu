@@ -196,12 +196,23 @@ __global__ void __launch_bounds__(kLossThreads) dynamics_loss_kernel(const LossA
     }
 }
 
-__global__ void dynamics_loss_reduce_kernel(const double* part, int nblocks, double sp, double si, float* losses) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) {
-        double tp = 0.0, ti = 0.0;
-        for (int i = 0; i < nblocks; ++i) { tp += part[2 * i]; ti += part[2 * i + 1]; }
-        losses[0] = (float)(tp * sp);
-        losses[1] = (float)(ti * si);
+// Sum of the per-block (prediction, integration) loss partials: thread t adds blocks t, t+256, ... in
+// order, then a fixed shared-memory tree; one block, deterministic.
+__global__ void __launch_bounds__(256) dynamics_loss_reduce_kernel(const double* part, int nblocks, double sp,
+                                                                   double si, float* losses) {
+    __shared__ double rp[256], ri[256];
+    const int t = threadIdx.x;
+    double tp = 0.0, ti = 0.0;
+    for (int i = t; i < nblocks; i += 256) { tp += part[2 * i]; ti += part[2 * i + 1]; }
+    rp[t] = tp; ri[t] = ti;
+    __syncthreads();
+    for (int h = 128; h > 0; h >>= 1) {
+        if (t < h) { rp[t] += rp[t + h]; ri[t] += ri[t + h]; }
+        __syncthreads();
+    }
+    if (t == 0) {
+        losses[0] = (float)(rp[0] * sp);
+        losses[1] = (float)(ri[0] * si);
     }
 }
 
@@ -261,6 +272,33 @@ __global__ void integrate_st_kernel(const float* xu, float* out, long long B, in
         float* o = out + (b * steps + s) * 7;
 #pragma unroll
         for (int i = 0; i < 7; ++i) o[i] = x[i];
+    }
+}
+
+// Prediction term alone, any output width: optax.l2_loss(pred, target).mean() = mean(0.5 d^2)
+// (scripts/train_nmpc.py:287) or mean |d|; writes the cotangent and the block partial like the kernels above.
+template <int KIND>
+__global__ void __launch_bounds__(kLossThreads) prediction_loss_kernel(const float* __restrict__ yp,
+                                                                       const float* __restrict__ y,
+                                                                       float* __restrict__ dy, double* part,
+                                                                       long long n, float inv) {
+    float psum = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float d = __ldg(yp + i) - __ldg(y + i);
+        if (KIND == 0) { psum += 0.5f * d * d; dy[i] = d * inv; }
+        else { psum += fabsf(d); dy[i] = signf(d) * inv; }
+    }
+    __shared__ double sp[kLossThreads / 32];
+    double dp = psum;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dp += __shfl_down_sync(0xffffffffu, dp, o);
+    if ((threadIdx.x & 31) == 0) sp[threadIdx.x >> 5] = dp;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tp = 0.0;
+        for (int w = 0; w < kLossThreads / 32; ++w) tp += sp[w];
+        part[2 * blockIdx.x] = tp;
+        part[2 * blockIdx.x + 1] = 0.0;
     }
 }
 
@@ -327,10 +365,36 @@ extern "C" int irbfn_dynamics_loss(int mode, const float* x, const float* y_pred
     else if (mode == IRBFN_LOSS_ST_ONEINT) e = O == 2 ? launch_loss<2, 2>(a, blocks, st) : launch_loss<2, 10>(a, blocks, st);
     else e = launch_loss<3, 10>(a, blocks, st);
     if (e != 0) return note_cuda_error("dynamics_loss_kernel", e);
-    dynamics_loss_reduce_kernel<<<1, 32, 0, st>>>((const double*)workspace, blocks, sp, si, losses);
+    dynamics_loss_reduce_kernel<<<1, 256, 0, st>>>((const double*)workspace, blocks, sp, si, losses);
     e = (int)cudaGetLastError();
     if (e != 0) return note_cuda_error("dynamics_loss_reduce_kernel", e);
     return IRBFN_OK;
+}
+
+extern "C" size_t irbfn_prediction_loss_workspace_bytes(int64_t B, int O) {
+    return (B <= 0 || O <= 0) ? 0 : (size_t)loss_blocks(B * O) * 2 * sizeof(double);
+}
+
+extern "C" int irbfn_prediction_loss(int kind, const float* y_pred, const float* y, float* dy, float* loss,
+                                     int64_t B, int O, int64_t global_batch, void* workspace,
+                                     size_t workspace_bytes, irbfn_stream_t stream) {
+    if (B <= 0 || O <= 0 || global_batch < B) return IRBFN_ERR_BAD_DIMS;
+    if (kind != IRBFN_PRED_LOSS_L2 && kind != IRBFN_PRED_LOSS_L1) return IRBFN_ERR_BAD_DIMS;
+    if (!y_pred || !y || !dy || !loss) return IRBFN_ERR_NULL_POINTER;
+    if (workspace_bytes < irbfn_prediction_loss_workspace_bytes(B, O) || !workspace) return IRBFN_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long n = (long long)B * O;
+    const double sp = 1.0 / ((double)global_batch * (double)O);
+    const int blocks = loss_blocks(n);
+    if (kind == IRBFN_PRED_LOSS_L2)
+        prediction_loss_kernel<0><<<blocks, kLossThreads, 0, st>>>(y_pred, y, dy, (double*)workspace, n, (float)sp);
+    else
+        prediction_loss_kernel<1><<<blocks, kLossThreads, 0, st>>>(y_pred, y, dy, (double*)workspace, n, (float)sp);
+    int e = (int)cudaGetLastError();
+    if (e != 0) return note_cuda_error("prediction_loss_kernel", e);
+    dynamics_loss_reduce_kernel<<<1, 256, 0, st>>>((const double*)workspace, blocks, sp, 0.0, loss);
+    e = (int)cudaGetLastError();
+    return e != 0 ? note_cuda_error("dynamics_loss_reduce_kernel", e) : IRBFN_OK;
 }
 
 extern "C" int irbfn_integrate(int model, const float* x_and_u, const float* dyn_params, float* states,

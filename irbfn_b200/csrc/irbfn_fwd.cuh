@@ -63,15 +63,7 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
 
         // ---- queries -> registers, packed in pairs over queries ----
         float2 x2[2][D];
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-            const long long qa = q0 + 2 * p, qb = qa + 1;
-#pragma unroll
-            for (int j = 0; j < D; ++j) {
-                x2[p][j].x = (qa < a.B && j < a.Dsrc) ? __ldg(a.x + qa * a.Dsrc + j) : 0.f;
-                x2[p][j].y = (qb < a.B && j < a.Dsrc) ? __ldg(a.x + qb * a.Dsrc + j) : 0.f;
-            }
-        }
+        load_queries4<D>(a.x, q0, a.B, a.Dsrc, x2);
 
         // ---- output accumulators start at the bias ----
         float2 y2[Q][OPS];
@@ -102,34 +94,7 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
                     gcol[rr * NT] = g;
                 }
             } else {
-                const int S = a.gd.S;
-                for (int rr = 0; rr < rc; ++rr) {
-                    const float one = (r0 + rr < a.gd.num_ranges) ? 1.f : 0.f;
-                    gcol[rr * NT] = make_float4(one, one, one, one);
-                }
-                const int rlim = min(rc, a.gd.num_ranges - r0);
-#pragma unroll
-                for (int j = 0; j < D; ++j) {
-                    if (j < S) {
-                        const float k2 = 2.0f * kLog2e * __ldg(a.gd.delta + j);
-                        const int ob = __ldg(a.gd.offset + j), oe = __ldg(a.gd.offset + j + 1);
-                        for (int i = ob; i < oe; ++i) {
-                            const float lb = __ldg(a.gd.lower + i), ub = __ldg(a.gd.upper + i);
-                            float4 f;
-                            f.x = gate_sigmoid(k2, x2[0][j].x - lb) * gate_sigmoid(k2, ub - x2[0][j].x);
-                            f.y = gate_sigmoid(k2, x2[0][j].y - lb) * gate_sigmoid(k2, ub - x2[0][j].y);
-                            f.z = gate_sigmoid(k2, x2[1][j].x - lb) * gate_sigmoid(k2, ub - x2[1][j].x);
-                            f.w = gate_sigmoid(k2, x2[1][j].y - lb) * gate_sigmoid(k2, ub - x2[1][j].y);
-                            for (int rr = 0; rr < rlim; ++rr) {
-                                if (__ldg(a.gd.ranges + (r0 + rr) * S + j) == i - ob) {
-                                    float4 g = gcol[rr * NT];
-                                    g.x *= f.x; g.y *= f.y; g.z *= f.z; g.w *= f.w;
-                                    gcol[rr * NT] = g;
-                                }
-                            }
-                        }
-                    }
-                }
+                gate_columns(a.gd, a.x, q0, a.B, a.Dsrc, r0, rc, gcol, NT);
             }
 
             for (int kch = 0; kch < n_kch; ++kch) {
@@ -329,11 +294,9 @@ inline int launch_fwd_inst(const FwdArgs& a, int grid, size_t smem, cudaStream_t
 
 template <int D, int OT>
 inline int launch_fwd_ot(const FwdArgs& a, int basis, int nt, int grid, size_t smem, cudaStream_t st) {
-    if (basis == IRBFN_BASIS_GAUSSIAN)
-        return nt == 512 ? launch_fwd_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 512>(a, grid, smem, st)
-                         : launch_fwd_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 256>(a, grid, smem, st);
-    return nt == 512 ? launch_fwd_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 512>(a, grid, smem, st)
-                     : launch_fwd_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 256>(a, grid, smem, st);
+    if (nt != 256) return (int)cudaErrorInvalidValue;   // the one compiled CTA size (fwd_threads_for)
+    if (basis == IRBFN_BASIS_GAUSSIAN) return launch_fwd_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 256>(a, grid, smem, st);
+    return launch_fwd_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 256>(a, grid, smem, st);
 }
 
 template <int D>

@@ -27,21 +27,33 @@ inline int fwd_ot_for(int ocur) {
     return 16;
 }
 
-// Split of the kernels of every region over gridDim.y for batches too small to give every SM a query
-// tile.  Returns the number of splits (1 = none) and the kernels per split (multiple of kFwdKT).
-inline int fwd_split(long long B, int K, int sms, int* k_per_split) {
-    const int Kp = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
-    *k_per_split = Kp;
+// Split of the kernels of every region over gridDim.y for batches that do not fill the device with one CTA
+// per 1,024-query tile.  Returns the number of splits (1 = none) and the kernels per split (multiple of
+// kFwdKT).  The choice minimises a cost model fitted to B200 measurements (scripts/dev_fwd_split.py), in
+// units of one (kernel tile, region) step of a CTA:
+//     cost(ns) = ceil(tiles * ns / sms) * (c0 + ceil(Kt / ns) * R) + (ns > 1 ? c_reduce : 0)
+// c0 = per-CTA fixed work (query load, gate, parameter staging, launch ramp), c_reduce = the partial-output
+// round trip.  CTAs beyond one per SM share an SM, which costs the same as a second round.
+inline int fwd_split(long long B, int R, int K, int sms, int* k_per_split) {
+    const int Kt = (K + kFwdKT - 1) / kFwdKT;
+    *k_per_split = Kt * kFwdKT;
     const long long tiles = (B + kFwdTQ - 1) / kFwdTQ;
-    if (tiles <= 0 || 2 * tiles > sms || Kp < 2 * kFwdKT) return 1;
-    const int want = (int)((sms + tiles - 1) / tiles);               // CTAs per query tile that fill the device
-    int kps = (Kp + want - 1) / want;
-    kps = ((kps + kFwdKT - 1) / kFwdKT) * kFwdKT;
-    if (kps < 2 * kFwdKT) kps = 2 * kFwdKT;                          // at least two kernel tiles per CTA
-    const int ns = (K + kps - 1) / kps;
-    if (ns <= 1) return 1;
-    *k_per_split = kps;
-    return ns;
+    if (tiles <= 0 || tiles >= 4ll * sms || Kt < 2 || sms <= 0) return 1;
+    const double c0 = 24.0 + R, c_reduce = 10.0;
+    double best = 0.0;
+    int best_kt = Kt;
+    for (int ns = 1; ns <= Kt && ns <= 64; ++ns) {
+        const int kt = (Kt + ns - 1) / ns;                 // kernel tiles per split
+        const int nsp = (Kt + kt - 1) / kt;                // splits that size gives
+        if (nsp != ns) continue;                           // same as a smaller ns already seen
+        const long long rounds = (tiles * nsp + sms - 1) / sms;
+        const double cost = (double)rounds * (c0 + (double)kt * R) + (nsp > 1 ? c_reduce : 0.0);
+        if (ns == 1 || cost < best) { best = cost; best_kt = kt; }
+    }
+    const int nsp = (Kt + best_kt - 1) / best_kt;
+    if (nsp <= 1) return 1;
+    *k_per_split = best_kt * kFwdKT;
+    return nsp;
 }
 
 struct FwdPlan {
@@ -175,8 +187,18 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     while (TQ >= 4 && bwdp_smem_floats(TQ, D, O, Kspan, Rspan, has_dhid, dht) * sizeof(float) > (size_t)smem_limit)
         TQ -= 4;
     if (TQ < 4) return false;
-    const long long ntiles = (B + TQ - 1) / TQ;
     long long splits = nchunks <= sms ? sms / nchunks : (4ll * sms + nchunks - 1) / nchunks;
+    if (splits < 1) splits = 1;
+    // Every split walks m = ceil(tiles / splits) tiles; shrink the tile so that the last of those rounds is
+    // full too (32,768 queries on 148 SMs: 147 tiles of 224 in one round instead of 128 tiles of 256).
+    if (B > 0) {
+        const long long m = (B + splits * TQ - 1) / (splits * TQ);
+        long long tqb = (B + splits * m - 1) / (splits * m);
+        tqb = (tqb + 3) & ~3ll;
+        if (tqb < 4) tqb = 4;
+        if (tqb < TQ) TQ = (int)tqb;
+    }
+    const long long ntiles = (B + TQ - 1) / TQ;
     if (splits > ntiles) splits = ntiles;
     if (splits < 1) splits = 1;
     p->OT = OT; p->NKP = NKP; p->NT = NT;

@@ -303,6 +303,32 @@ def dynamics_loss(mode: int, x, y_pred, y, dyn_params, global_batch: Optional[in
     return losses, dy
 
 
+def prediction_loss(y_pred, y, global_batch: Optional[int] = None, kind: str = "l2",
+                    dy: Optional[torch.Tensor] = None, loss: Optional[torch.Tensor] = None):
+    """Prediction loss and its cotangent in one launch (irbfn_prediction_loss): ``kind`` "l2" is
+    optax.l2_loss(...).mean() = mean(0.5 d^2), "l1" is mean |d|; the mean runs over ``global_batch`` rows.
+    Returns (loss, dy): a one-element device tensor (this shard's part) and dloss/dy_pred (B,O)."""
+    lib = _lib.load()
+    _chk(y_pred, "y_pred")
+    B, O = y_pred.shape
+    _chk(y, "y", (B, O))
+    kinds = {"l2": 0, "l1": 1}
+    if kind not in kinds:
+        raise ValueError("loss must be 'l2' or 'l1'")
+    gb = int(global_batch) if global_batch is not None else B
+    dy = dy if dy is not None else torch.empty((B, O), device=y_pred.device, dtype=torch.float32)
+    loss = loss if loss is not None else torch.empty(1, device=y_pred.device, dtype=torch.float32)
+    _chk(dy, "dy", (B, O))
+    _chk(loss, "loss", (1,))
+    with torch.cuda.device(y_pred.device):
+        nbytes = lib.irbfn_prediction_loss_workspace_bytes(B, O)
+        ws = _workspace(nbytes, y_pred.device)
+        rc = lib.irbfn_prediction_loss(kinds[kind], _ptr(y_pred), _ptr(y), _ptr(dy), _ptr(loss), B, O, gb,
+                                       _ptr(ws), nbytes, _stream())
+    _lib.check(rc, "irbfn_prediction_loss")
+    return loss, dy
+
+
 _DYN_OUT = {_lib.DYN_FRENET_MULT: (5, 8), _lib.DYN_FRENET_ONESTEP_AUX: (6,), _lib.DYN_ST_MULT: (5, 7),
             _lib.DYN_ST_ONESTEP_AUX: (7,)}
 

@@ -148,7 +148,8 @@ def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch:
         state.loss_terms = terms          # [pred_loss, int_loss] of this shard (device)
         lval = terms.sum()
     else:
-        lval, dy = loss_and_cotangent(y_pred, y, gb, loss)
+        lv, dy = ops.prediction_loss(y_pred, y, gb, loss)     # one launch; loss_and_cotangent is its torch spelling
+        lval = lv[0]
     ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gd=gd, basis=m._basis,
                  grad_mask=state.mask, flat_out=state.grad)
     if gb != x.shape[0]:

@@ -150,3 +150,34 @@ def test_train_step_with_frenet_dynamics_loss_matches_oracle_chain(cuda_device):
     assert abs(float(lval) - loss) <= 1e-4 * abs(loss)
     for name in ("centers", "log_sigs", "kernel", "bias"):
         assert rel_l2(state.gviews[name].cpu().numpy(), ref[name]) <= 2e-4, name
+
+
+@pytest.mark.parametrize("kind", ["l2", "l1"])
+@pytest.mark.parametrize("B,O,gb", [(1, 2, 1), (1000, 10, 4000), (262144, 2, 262144), (33333, 16, 33333), (5, 37, 5)])
+def test_prediction_loss_matches_float64(kind, B, O, gb, cuda_device):
+    """irbfn_prediction_loss against the float64 spelling of optax.l2_loss(...).mean() / jnp.abs(...).mean()
+    (scripts/train_nmpc.py:287, scripts/train_nmpc_frenet.py:347): loss to 1e-6 relative, the cotangent exactly
+    the float32 formula, and bit-identical run to run."""
+    from irbfn_b200.train import loss_and_cotangent
+    rng = np.random.default_rng(B + O)
+    yp, y = rng.normal(size=(B, O)).astype(np.float32), rng.normal(size=(B, O)).astype(np.float32)
+    if B > 3:
+        yp[3] = y[3]                                    # exact ties: sign(0) = 0
+    d = yp.astype(np.float64) - y.astype(np.float64)
+    want = (0.5 * d * d if kind == "l2" else np.abs(d)).sum() / (gb * O)
+    ypd, yd = torch.from_numpy(yp).to(cuda_device), torch.from_numpy(y).to(cuda_device)
+    loss, dy = ops.prediction_loss(ypd, yd, gb, kind)
+    loss2, dy2 = ops.prediction_loss(ypd, yd, gb, kind)
+    torch.cuda.synchronize()
+    assert abs(float(loss[0]) - want) <= 1e-6 * abs(want) + 1e-12
+    assert torch.equal(loss, loss2) and torch.equal(dy, dy2)
+    inv = np.float32(1.0 / (float(gb) * O))
+    dy_want = (yp - y) * inv if kind == "l2" else np.sign(yp - y) * inv
+    assert np.array_equal(dy.cpu().numpy(), dy_want.astype(np.float32))
+    lt, dyt = loss_and_cotangent(ypd, yd, gb, kind)     # the torch spelling kept for the CPU tests
+    assert abs(float(lt) - want) <= 2e-5 * abs(want) + 1e-12
+    assert torch.allclose(dyt, dy, rtol=1e-6, atol=0)
+    with pytest.raises(ValueError):
+        ops.prediction_loss(ypd, yd, gb, "huber")
+    with pytest.raises(Exception):
+        ops.prediction_loss(ypd, yd, B - 1 if B > 1 else 0, kind)   # global batch below the shard
