@@ -230,6 +230,24 @@ int irbfn_prediction_loss(int kind, const float* y_pred, const float* y, float* 
                           irbfn_stream_t stream);
 
 /*
+ * Optimiser update on a flat fp32 parameter buffer: optax.chain(clip_by_global_norm(max_norm), adam(lr, b1,
+ * b2, eps)) as built at scripts/train_nmpc.py:231-236 and applied by state.apply_gradients (:299).  optax is a
+ * dependency of the reference (pyproject.toml, unpinned), not part of it; the update follows optax's published
+ * clip_by_global_norm / scale_by_adam / scale(-lr) definitions.
+ *   params, grad, mu, nu: device arrays of n floats, updated in place (grad is left clipped).
+ *   step_count: ONE device double, the Adam count; incremented by this call before use (so the call is
+ *   CUDA-graph capturable).  max_norm <= 0 disables clipping.  grad_norm: device float out or NULL
+ *   (the pre-clip global norm).  The norm is reduced in a fixed order in fp64: deterministic.
+ *   Hyper-parameters are doubles and are rounded to float32 one by one, (1 - b) included, the way JAX
+ *   rounds weak-typed Python scalars.
+ */
+size_t irbfn_clip_adam_workspace_bytes(int64_t n);
+
+int irbfn_clip_adam(float* params, float* grad, float* mu, float* nu, int64_t n, double* step_count, double lr,
+                    double b1, double b2, double eps, double max_norm, float* grad_norm, void* workspace,
+                    size_t workspace_bytes, irbfn_stream_t stream);
+
+/*
  * Plain rollouts (what irbfn_planner.py:212-214,510-518 and the losses call):
  *   IRBFN_DYN_FRENET_MULT         integrate_frenet_mult       dynamics.py:284-290  (B,18) -> (B,5,8)
  *   IRBFN_DYN_FRENET_ONESTEP_AUX  dynamic_frenet_onestep_aux  dynamics.py:293-383  (B,width>=8) -> (B,6)

@@ -36,6 +36,7 @@ EXPORTED_SYMBOLS = (
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
     "irbfn_gather_rows", "irbfn_grid_index", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
     "irbfn_prediction_loss_workspace_bytes", "irbfn_prediction_loss",
+    "irbfn_clip_adam_workspace_bytes", "irbfn_clip_adam",
 )
 
 
@@ -101,6 +102,11 @@ def load():
     lib.irbfn_prediction_loss_workspace_bytes.argtypes = [i64, i]
     lib.irbfn_prediction_loss.restype = i
     lib.irbfn_prediction_loss.argtypes = [i, p, p, p, p, i64, i, i64, p, sz, p]
+    lib.irbfn_clip_adam_workspace_bytes.restype = sz
+    lib.irbfn_clip_adam_workspace_bytes.argtypes = [i64]
+    lib.irbfn_clip_adam.restype = i
+    lib.irbfn_clip_adam.argtypes = [p, p, p, p, i64, p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
+                                    p, p, sz, p]
     lib.irbfn_dynamics_loss.restype = i
     lib.irbfn_dynamics_loss.argtypes = [i, p, p, p, C.POINTER(C.c_float), p, p, i64, i, i, i64, p, sz, p]
     lib.irbfn_integrate.restype = i

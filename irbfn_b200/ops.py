@@ -329,6 +329,29 @@ def prediction_loss(y_pred, y, global_batch: Optional[int] = None, kind: str = "
     return loss, dy
 
 
+def clip_adam_(params, grad, mu, nu, step_count, lr: float, b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8,
+               max_norm: float = 0.0, grad_norm: Optional[torch.Tensor] = None):
+    """optax.chain(clip_by_global_norm(max_norm), adam(lr)) on flat fp32 device buffers, in place
+    (irbfn_clip_adam: two launches).  ``step_count`` is a float64 device scalar, incremented by the call.
+    Returns the pre-clip global gradient norm (one-element device tensor)."""
+    lib = _lib.load()
+    n = params.numel()
+    for t, name in ((params, "params"), (grad, "grad"), (mu, "mu"), (nu, "nu")):
+        _chk(t, name, (n,))
+    _chk(step_count, "step_count", dtype=torch.float64)
+    if step_count.numel() != 1:
+        raise ValueError("step_count must be a one-element float64 CUDA tensor")
+    grad_norm = grad_norm if grad_norm is not None else torch.empty(1, device=params.device, dtype=torch.float32)
+    _chk(grad_norm, "grad_norm", (1,))
+    with torch.cuda.device(params.device):
+        nbytes = lib.irbfn_clip_adam_workspace_bytes(n)
+        ws = _workspace(nbytes, params.device)
+        rc = lib.irbfn_clip_adam(_ptr(params), _ptr(grad), _ptr(mu), _ptr(nu), n, _ptr(step_count), lr, b1, b2, eps,
+                                 max_norm, _ptr(grad_norm), _ptr(ws), nbytes, _stream())
+    _lib.check(rc, "irbfn_clip_adam")
+    return grad_norm
+
+
 _DYN_OUT = {_lib.DYN_FRENET_MULT: (5, 8), _lib.DYN_FRENET_ONESTEP_AUX: (6,), _lib.DYN_ST_MULT: (5, 7),
             _lib.DYN_ST_ONESTEP_AUX: (7,)}
 

@@ -38,7 +38,7 @@ class TrainState:
         self.apply_fn = module.apply
         self.lr, self.max_grad_norm, self.b1, self.b2, self.eps = lr, max_grad_norm, b1, b2, eps
         self.step = 0
-        self.step_t = None            # device copy of the step count, used once the step is graph-captured
+        self.step_t = None            # device copy of the Adam count (float64), created below
         R, K, D, O = module.num_regions, module.num_kernels, module.in_features, module.out_features
         rb = p.get("rbf_list", {})
         self.train_centers = "centers" in rb
@@ -69,6 +69,8 @@ class TrainState:
         self.mask = (ops.GRAD_CENTERS if self.train_centers else 0) | \
                     (ops.GRAD_LOG_SIGS if self.train_log_sigs else 0) | ops.GRAD_KERNEL
         self.device = device
+        self.step_t = torch.zeros((), device=device, dtype=torch.float64)
+        self.grad_norm = torch.zeros(1, device=device, dtype=torch.float32)
         self.dyn_params = ops.default_dyn_params()   # scripts/train_nmpc_frenet.py:322-338
         self.loss_terms = None
 
@@ -111,24 +113,25 @@ DYNAMICS_LOSSES = {"frenet_oneint": 0, "frenet_fullint": 1, "st_oneint": 2, "st_
 
 
 def clip_and_adam_(state: TrainState):
-    """optax.chain(clip_by_global_norm(max_norm), adam(lr)) on the flat buffers, in place."""
-    g = state.grad
-    gnorm = torch.linalg.vector_norm(g)
-    scale = torch.clamp(state.max_grad_norm / torch.clamp(gnorm, min=1e-30), max=1.0)  # optax: g * min(1, c/|g|)
-    g.mul_(scale)
+    """optax.chain(clip_by_global_norm(max_norm), adam(lr)) on the flat buffers, in place: two launches
+    (irbfn_clip_adam).  The Adam count lives on the device (``state.step_t``), so the call can sit inside a
+    CUDA graph; ``state.step`` is its host mirror.  Returns the pre-clip global gradient norm (device)."""
     state.step += 1
-    state.mu.mul_(state.b1).add_(g, alpha=1 - state.b1)
-    state.nu.mul_(state.b2).addcmul_(g, g, value=1 - state.b2)
-    if state.step_t is None:
-        bc1 = 1 - state.b1 ** state.step
-        bc2 = 1 - state.b2 ** state.step
-    else:
-        # the step count lives on the device so that a captured CUDA graph of this update stays valid
-        # from replay to replay (GraphedTrainStep); float64 keeps b2 ** t exact enough for t ~ 1e6
-        state.step_t += 1
-        bc1 = (1 - torch.pow(torch.full_like(state.step_t, state.b1), state.step_t)).float()
-        bc2 = (1 - torch.pow(torch.full_like(state.step_t, state.b2), state.step_t)).float()
-    state.flat.addcdiv_(state.mu / bc1, (state.nu / bc2).sqrt_().add_(state.eps), value=-state.lr)
+    ops.clip_adam_(state.flat, state.grad, state.mu, state.nu, state.step_t.view(1), state.lr, state.b1, state.b2,
+                   state.eps, state.max_grad_norm, state.grad_norm)
+    return state.grad_norm[0]
+
+
+def clip_and_adam_torch_(flat, grad, mu, nu, step: int, lr, b1=0.9, b2=0.999, eps=1e-8, max_norm=1.0):
+    """The same update spelled with torch element-wise ops on any device (host-side tests compare the
+    kernel against this and against oracle/optim_oracle.py); ``step`` is the count AFTER the increment."""
+    gnorm = torch.linalg.vector_norm(grad)
+    if max_norm > 0 and not bool(gnorm < max_norm):
+        grad.div_(gnorm).mul_(max_norm)
+    mu.mul_(b1).add_(grad, alpha=1 - b1)
+    nu.mul_(b2).addcmul_(grad, grad, value=1 - b2)
+    bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step
+    flat.addcdiv_(mu / bc1, (nu / bc2).sqrt_().add_(eps), value=-lr)
     return gnorm
 
 
@@ -187,8 +190,6 @@ class GraphedTrainStep:
         self.global_batch = int(global_batch) if global_batch is not None else int(shard_rows)
         self.x = torch.zeros((shard_rows, m.in_features), device=dev)
         self.y = torch.zeros((shard_rows, m.out_features), device=dev)
-        if state.step_t is None:
-            state.step_t = torch.full((), float(state.step), device=dev, dtype=torch.float64)
         snap = (state.flat.clone(), state.mu.clone(), state.nu.clone(), state.step_t.clone(), state.step)
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
