@@ -13,7 +13,8 @@ import torch
 class HostPipeline:
     NBUF = 3
 
-    def __init__(self, device, in_features: int, out_features: int, chunk: int = 1 << 17, copy_streams: int = 1):
+    def __init__(self, device, in_features: int, out_features: int, chunk: int = 1 << 17, copy_streams: int = 1,
+                 run_streams: int = 1):
         self.device = torch.device(device)
         self.D, self.O, self.chunk = in_features, out_features, int(chunk)
         # Optionally cut each chunk's upload into `copy_streams` pieces on separate streams (separate DMA
@@ -23,7 +24,13 @@ class HostPipeline:
         self.ncopy = max(1, int(copy_streams))
         self.s_ins = [torch.cuda.Stream(self.device) for _ in range(self.ncopy)]
         self.s_in = self.s_ins[0]
-        self.s_run = torch.cuda.Stream(self.device)
+        # Chunk kernels alternate over `run_streams` streams: with chunks smaller than one wave of query tiles,
+        # several chunk kernels share the device, so the pipeline fills after a short first copy and the SMs
+        # never wait for a whole wave's upload.
+        self.nrun = max(1, int(run_streams))
+        self.NBUF = max(3, self.nrun + 2)
+        self.s_runs = [torch.cuda.Stream(self.device) for _ in range(self.nrun)]
+        self.s_run = self.s_runs[0]
         self.s_out = torch.cuda.Stream(self.device)
         self.xd = [torch.empty((self.chunk, self.D), device=self.device) for _ in range(self.NBUF)]
         self.yd = [torch.empty((self.chunk, self.O), device=self.device) for _ in range(self.NBUF)]
@@ -90,7 +97,7 @@ class HostPipeline:
 
     def _enqueue(self, xin, out, B, launch):
         cur = torch.cuda.current_stream(self.device)
-        for s in (*self.s_ins, self.s_run, self.s_out):
+        for s in (*self.s_ins, *self.s_runs, self.s_out):
             s.wait_stream(cur)
         n = (B + self.chunk - 1) // self.chunk
         for i in range(n):
@@ -106,13 +113,14 @@ class HostPipeline:
                     if e > a:
                         self.xd[b][a:e].copy_(xin[lo + a:lo + e], non_blocking=True)
                     self.ev_in[b][k].record(s_in)
-            with torch.cuda.stream(self.s_run):
+            s_run = self.s_runs[i % self.nrun]
+            with torch.cuda.stream(s_run):
                 for k in range(self.ncopy):
-                    self.s_run.wait_event(self.ev_in[b][k])
+                    s_run.wait_event(self.ev_in[b][k])
                 if i >= self.NBUF:
-                    self.s_run.wait_event(self.ev_out[b])     # copy-out that read yd[b] is done
+                    s_run.wait_event(self.ev_out[b])          # copy-out that read yd[b] is done
                 launch(self.xd[b][:m], self.yd[b][:m])
-                self.ev_run[b].record(self.s_run)
+                self.ev_run[b].record(s_run)
             with torch.cuda.stream(self.s_out):
                 self.s_out.wait_event(self.ev_run[b])
                 out[lo:hi].copy_(self.yd[b][:m], non_blocking=True)

@@ -285,7 +285,7 @@ class WCRBFNet(_IrbfnModule):
                             want_y=with_value)
 
     def apply_host(self, params, x, out=None, chunk: Optional[int] = None, copy_streams: int = 1,
-                   graph: bool = False):
+                   graph: bool = False, run_streams: int = 1):
         """Host-buffer entry point: x is a NumPy array or CPU tensor (B,D); the batch is cut into
         chunks whose host->device copy, kernel and device->host copy overlap on three streams.
         Returns a NumPy array (or fills ``out``, a pinned CPU tensor, and returns it)."""
@@ -299,12 +299,14 @@ class WCRBFNet(_IrbfnModule):
             # one full wave of the persistent forward per chunk: (SM count) query tiles of 1,024, so no
             # chunk leaves SMs idle (2^17 queries = 128 tiles on 148 SMs cost 13 % of the kernel time)
             chunk = torch.cuda.get_device_properties(device).multi_processor_count * 1024
-        key = ("pipe", str(device), chunk, copy_streams)
+        key = ("pipe", str(device), chunk, copy_streams, run_streams)
         if key not in self._const:
-            self._const[key] = HostPipeline(device, self.in_features, self.out_features, chunk, copy_streams)
+            self._const[key] = HostPipeline(device, self.in_features, self.out_features, chunk, copy_streams,
+                                            run_streams)
         pipe = self._const[key]
         return pipe.run(x, out, lambda xs, ys: ops.forward(xs, centers, log_sigs, kernel, bias, gd=gd,
-                                                           basis=self._basis, out=ys), graph=graph,
+                                                           basis=self._basis, out=ys, split=run_streams == 1),
+                        graph=graph,
                         graph_key=(centers.data_ptr(), log_sigs.data_ptr(), kernel.data_ptr(), bias.data_ptr()))
 
 

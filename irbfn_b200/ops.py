@@ -90,8 +90,10 @@ class GatePack:
 
 def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: GatePack = None,
             basis: int = BASIS_GAUSSIAN, want_y: bool = True, want_hidden: bool = False,
-            out=None):
-    """y (B,O) and/or hidden (B,K) of the fused IRBFN forward (irbfn_forward)."""
+            out=None, split: bool = True):
+    """y (B,O) and/or hidden (B,K) of the fused IRBFN forward (irbfn_forward).  ``split=False`` withholds
+    the workspace, so a small batch runs as ONE CTA per query tile instead of spreading its kernels over
+    the device -- what a caller wants when it keeps the device busy with several launches at once."""
     lib = _lib.load()
     _chk(x, "x")
     B, D = x.shape
@@ -122,7 +124,7 @@ def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: Gate
     if B == 0:  # empty tensors have no storage to point at
         return (y, hidden) if want_y and want_hidden else (y if want_y else hidden)
     with torch.cuda.device(x.device):
-        nbytes = lib.irbfn_forward_workspace_bytes(B, R, K, D, O, 1 if gd is not None else 0)
+        nbytes = lib.irbfn_forward_workspace_bytes(B, R, K, D, O, 1 if gd is not None else 0) if split else 0
         ws = _workspace(nbytes, x.device)       # partial readouts of the small-batch split-K path
         rc = lib.irbfn_forward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias),
                                _ptr(gate), gd.ref() if gd is not None else None, _ptr(y),

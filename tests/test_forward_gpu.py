@@ -257,11 +257,15 @@ def test_host_pipeline_variants_agree(cuda_device):
     xh = torch.from_numpy(x.copy()).pin_memory()
     yh = torch.empty((5000, 2)).pin_memory()
     ref = net.apply(dp, torch.from_numpy(x).to(cuda_device)).cpu()
-    for kw in (dict(), dict(copy_streams=2), dict(graph=True), dict(graph=True)):
+    for kw in (dict(), dict(copy_streams=2), dict(graph=True), dict(graph=True), dict(run_streams=2),
+               dict(run_streams=3, graph=True), dict(run_streams=3, graph=True)):
         yh.zero_()
         net.apply_host(dp, xh, out=yh, chunk=2048, **kw)
         torch.cuda.synchronize()
-        assert torch.equal(yh, ref), kw
+        if kw.get("run_streams", 1) == 1:
+            assert torch.equal(yh, ref), kw
+        else:   # several chunk kernels in flight run unsplit (one CTA per tile): another summation order
+            assert torch.allclose(yh, ref, rtol=0, atol=2e-6 * float(ref.abs().max())), kw
     xh.mul_(0.5)                                      # new values, same buffers: the graph must pick them up
     ref2 = net.apply(dp, xh.to(cuda_device)).cpu()
     net.apply_host(dp, xh, out=yh, chunk=2048, graph=True)
