@@ -357,7 +357,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             a.dy = dy; a.dhidden = dhidden;
             a.part = (float*)(ws + L.part_off);
             a.B = B; a.R = R; a.K = K; a.Dsrc = D; a.O = Oeff; a.o0 = o0; a.ocur = ocur;
-            a.nchunks = pp.nchunks; a.splits = pp.splits; a.pairs_per_chunk = pp.pairs_per_chunk;
+            a.nchunks = pp.nchunks; a.splits = pp.splits; a.pairs_per_chunk = pp.pairs_per_chunk; a.ppw = pp.ppw;
             a.TQ = pp.TQ; a.Kspan = pp.Kspan; a.Rspan = pp.Rspan;
             a.write_cls = first ? 1 : 0;
             const int grid = pp.nchunks * pp.splits;

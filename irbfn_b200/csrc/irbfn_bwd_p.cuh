@@ -25,6 +25,7 @@
 //     applies the 2 exp(-2 log_sig) factor.  Fixed partition + fixed order = deterministic.
 #pragma once
 #include "irbfn_common.cuh"
+#include "irbfn_plan.h"
 
 namespace irbfn {
 
@@ -42,6 +43,7 @@ struct BwdPArgs {
     int o0, ocur;           // dW column window of this launch
     int nchunks, splits;
     int pairs_per_chunk;    // Pc
+    int ppw;                // kernel pairs per warp: lanes >= ppw hold none (32: pair slot = thread index)
     int TQ;                 // queries per tile
     int Kspan;              // columns of the dh table (even)
     int Rspan;              // columns of the gate table, + 1 zero column at index Rspan
@@ -60,12 +62,14 @@ __host__ __device__ constexpr int bwdp_xs(int D) { return ((D + 3) / 4) * 4; }
 __host__ __device__ inline int bwdp_ds(int O) { return O <= 0 ? 0 : (O <= 2 ? 2 : ((O + 3) / 4) * 4); }
 
 template <int D, int OT, int BASIS, int NKP, int DHT>
-__global__ void __launch_bounds__(320, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
+__global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 320, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
     constexpr int OTS = OT > 0 ? OT : 1;
     constexpr int PW = D + 1 + OT;
     constexpr int XS = bwdp_xs(D);
     const int NT = blockDim.x;
     const int tid = threadIdx.x;
+    const bool lane_ok = (tid & 31) < a.ppw;
+    const int pslot = (tid >> 5) * a.ppw + (tid & 31);   // == tid when ppw == 32
     const int chunk = blockIdx.x % a.nchunks;
     const int split = blockIdx.x / a.nchunks;
     const int RK = a.R * a.K;
@@ -98,12 +102,12 @@ __global__ void __launch_bounds__(320, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
     bool contig[NKP];
 #pragma unroll
     for (int p = 0; p < NKP; ++p) {
-        const int pl = tid + p * NT;  // pair slot within the chunk
+        const int pl = pslot + p * NT;  // pair slot within the chunk
         sc2[p] = make_float2(0.f, 0.f);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int f = f_lo + 2 * pl + h;
-            const bool valid = pl < a.pairs_per_chunk && f < f_hi;
+            const bool valid = lane_ok && pl < a.pairs_per_chunk && f < f_hi;
             const int fc = valid ? f : f_lo;
             const int r = fc / K, k = fc - r * K;
             kidx[p][h] = k_direct ? k : (fc - f_lo);
@@ -274,11 +278,11 @@ __global__ void __launch_bounds__(320, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
     float* part = a.part + (size_t)split * RK * PW;
 #pragma unroll
     for (int p = 0; p < NKP; ++p) {
-        const int pl = tid + p * NT;
+        const int pl = pslot + p * NT;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int f = f_lo + 2 * pl + h;
-            if (pl < a.pairs_per_chunk && f < f_hi) {
+            if (lane_ok && pl < a.pairs_per_chunk && f < f_hi) {
                 float* o = part + (size_t)f * PW;
                 if (a.write_cls) {
 #pragma unroll
@@ -293,7 +297,7 @@ __global__ void __launch_bounds__(320, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
 }
 
 // kernel pairs per thread as a function of the output window: keeps the accumulators in registers
-__host__ __device__ constexpr int bwd_p_nkp_for(int OT) { return OT <= 4 ? 2 : 1; }
+__host__ __device__ constexpr int bwd_p_nkp_for(int OT) { return OT <= 4 ? IRBFN_BWDP_NKP_NARROW : 1; }
 
 template <int D, int OT, int BASIS, int DHT>
 inline int launch_bwd_p_inst(const BwdPArgs& a, int grid, int nt, size_t smem, cudaStream_t st) {

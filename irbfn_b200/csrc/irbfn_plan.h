@@ -136,11 +136,18 @@ inline bool plan_bwd_x(int R, int K, int D, int OT, int smem_limit, FwdPlan* p) 
 // backward P (parameter gradients): kernel pairs per thread, chunks of pairs per CTA,
 // query splits, tile size.  Must match irbfn_bwd_p.cuh.
 // ---------------------------------------------------------------------------------------
-inline int bwdp_nkp_for(int OT) { return OT <= 4 ? 2 : 1; }
-constexpr int kBwdPMaxThreads = 320;   // __launch_bounds__ of irbfn_bwd_p_kernel
+#ifndef IRBFN_BWDP_NKP_NARROW
+#define IRBFN_BWDP_NKP_NARROW 1
+#endif
+inline int bwdp_nkp_for(int OT) { return OT <= 4 ? IRBFN_BWDP_NKP_NARROW : 1; }
+// Threads per CTA: a thread that holds ONE kernel pair and few outputs needs ~95 registers, so 640 threads
+// (20 warps, five on every SM sub-partition) fit one SM; the wider variants keep 320.
+inline int bwdp_max_threads(int OT) { return (bwdp_nkp_for(OT) == 1 && OT <= 4) ? 640 : 320; }
+constexpr int kBwdPMaxThreads = 320;   // the wide variants' __launch_bounds__
 
 struct BwdPPlan {
     int OT, NKP, NT;
+    int ppw;             // kernel pairs per warp (32 = every lane holds pairs)
     int nchunks, pairs_per_chunk, splits;
     int TQ, Kspan, Rspan;
     int PW;              // partial-sum row width: D + 1 + OT
@@ -167,11 +174,23 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     if (RK <= 0 || RK > (1ll << 30)) return false;
     const int P = (int)((RK + 1) / 2);
     const int NKP = bwdp_nkp_for(OT);
-    const int per_cta = kBwdPMaxThreads * NKP;
+    const int maxt = bwdp_max_threads(OT);
+    const int per_cta = maxt * NKP;
     const int nchunks = (P + per_cta - 1) / per_cta;
     const int Pc = (P + nchunks - 1) / nchunks;
     int NT = (((Pc + NKP - 1) / NKP + 31) / 32) * 32;
-    if (NT > kBwdPMaxThreads) NT = kBwdPMaxThreads;
+    if (NT > maxt) NT = maxt;
+    int ppw = 32;
+    if (NKP == 1 && maxt == 640) {
+        // The SM places warp w on sub-partition w % 4: a warp count that is a multiple of four with the pairs
+        // spread evenly over the warps keeps the four FP32 pipes equally loaded.  (600 pairs on 10 warps of 2
+        // pairs per lane put 3/3/2/1.4 warps of work on the four pipes; the barrier per query tile then held
+        // the kernel to the slowest: 65 % FMA-pipe utilisation in ncu with math_pipe_throttle AND barrier on top.)
+        int nw = (((Pc + 31) / 32 + 3) / 4) * 4;
+        if (nw * 32 > maxt) nw = maxt / 32;
+        ppw = (Pc + nw - 1) / nw;
+        NT = nw * 32;
+    }
     const long long flen = 2ll * Pc;
     int Kspan = flen >= K ? K : (int)flen;
     Kspan = (Kspan + 1) & ~1;
@@ -187,7 +206,8 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     while (TQ >= 4 && bwdp_smem_floats(TQ, D, O, Kspan, Rspan, has_dhid, dht) * sizeof(float) > (size_t)smem_limit)
         TQ -= 4;
     if (TQ < 4) return false;
-    long long splits = nchunks <= sms ? sms / nchunks : (4ll * sms + nchunks - 1) / nchunks;
+    const int slots = sms;
+    long long splits = nchunks <= slots ? slots / nchunks : (4ll * slots + nchunks - 1) / nchunks;
     if (splits < 1) splits = 1;
     // Every split walks m = ceil(tiles / splits) tiles; shrink the tile so that the last of those rounds is
     // full too (32,768 queries on 148 SMs: 147 tiles of 224 in one round instead of 128 tiles of 256).
@@ -201,7 +221,7 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     const long long ntiles = (B + TQ - 1) / TQ;
     if (splits > ntiles) splits = ntiles;
     if (splits < 1) splits = 1;
-    p->OT = OT; p->NKP = NKP; p->NT = NT;
+    p->OT = OT; p->NKP = NKP; p->NT = NT; p->ppw = ppw;
     p->nchunks = nchunks; p->pairs_per_chunk = Pc; p->splits = (int)splits;
     p->TQ = TQ; p->Kspan = Kspan; p->Rspan = Rspan;
     p->PW = D + 1 + OT;
