@@ -62,7 +62,7 @@ __host__ __device__ constexpr int bwdp_xs(int D) { return ((D + 3) / 4) * 4; }
 __host__ __device__ inline int bwdp_ds(int O) { return O <= 0 ? 0 : (O <= 2 ? 2 : ((O + 3) / 4) * 4); }
 
 template <int D, int OT, int BASIS, int NKP, int DHT>
-__global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 320, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
+__global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
     constexpr int OTS = OT > 0 ? OT : 1;
     constexpr int PW = D + 1 + OT;
     constexpr int XS = bwdp_xs(D);

@@ -141,9 +141,9 @@ inline bool plan_bwd_x(int R, int K, int D, int OT, int smem_limit, FwdPlan* p) 
 #endif
 inline int bwdp_nkp_for(int OT) { return OT <= 4 ? IRBFN_BWDP_NKP_NARROW : 1; }
 // Threads per CTA: a thread that holds ONE kernel pair and few outputs needs ~95 registers, so 640 threads
-// (20 warps, five on every SM sub-partition) fit one SM; the wider variants keep 320.
-inline int bwdp_max_threads(int OT) { return (bwdp_nkp_for(OT) == 1 && OT <= 4) ? 640 : 320; }
-constexpr int kBwdPMaxThreads = 320;   // the wide variants' __launch_bounds__
+// (20 warps, five on every SM sub-partition) fit one SM; the wide-output variants (~165 registers) get 384
+// (12 warps, three per sub-partition).
+inline int bwdp_max_threads(int OT) { return (bwdp_nkp_for(OT) == 1 && OT <= 4) ? 640 : 384; }
 
 struct BwdPPlan {
     int OT, NKP, NT;
@@ -181,7 +181,7 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     int NT = (((Pc + NKP - 1) / NKP + 31) / 32) * 32;
     if (NT > maxt) NT = maxt;
     int ppw = 32;
-    if (NKP == 1 && maxt == 640) {
+    if (NKP == 1) {
         // The SM places warp w on sub-partition w % 4: a warp count that is a multiple of four with the pairs
         // spread evenly over the warps keeps the four FP32 pipes equally loaded.  (600 pairs on 10 warps of 2
         // pairs per lane put 3/3/2/1.4 warps of work on the four pipes; the barrier per query tile then held
