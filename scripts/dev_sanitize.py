@@ -8,7 +8,8 @@ from test_forward_gpu import _synthetic, _gd, _t
 
 dev = torch.device("cuda:0")
 P = ops.default_dyn_params()
-for (B, R, K, D, O) in [(700, 3, 37, 5, 3), (2100, 2, 300, 8, 10), (300, 12, 100, 8, 2), (130, 16, 2048, 8, 2), (50, 2, 9, 3, 18)]:
+for (B, R, K, D, O) in [(700, 3, 37, 5, 3), (2100, 2, 300, 8, 10), (300, 12, 100, 8, 2), (130, 16, 2048, 8, 2), (50, 2, 9, 3, 18),
+                        (260, 4, 512, 6, 16), (40000, 12, 100, 8, 2)]:
     cfg, p, x = _synthetic(1, B, R, K, D, O)
     xs, c, ls, W, b = (_t(a, dev) for a in (x, p["centers"], p["log_sigs"], p["kernel"], p["bias"]))
     gd = _gd(cfg, dev)
@@ -35,5 +36,13 @@ ops.nearest_row(torch.rand((70000, 8), device=dev)[:5000].contiguous(), X[:1001]
 gk = ops.GridKeys([np.linspace(0, 1, n) for n in (5, 1, 9)], dev)
 ops.grid_index(torch.rand((1000, 3), device=dev), gk)
 ops.softmax_gate(torch.rand((100, 8), device=dev), torch.rand((8, 50), device=dev), torch.rand(50, device=dev))
+for kind in ("l2", "l1"):
+    ops.prediction_loss(torch.randn((1234, 10), device=dev), torch.randn((1234, 10), device=dev), kind=kind)
+n = 11003
+prm, g, mu, nu = (torch.randn(n, device=dev) for _ in range(4))
+nu.abs_()
+cnt = torch.zeros(1, device=dev, dtype=torch.float64)
+for max_norm in (0.0, 1.0):
+    ops.clip_adam_(prm, g, mu, nu, cnt, 1e-3, max_norm=max_norm)
 torch.cuda.synchronize()
 print("all kernels ran")
