@@ -199,7 +199,7 @@ def main():
         return run_reference(args)
 
     import torch
-    from irbfn_b200 import ops, parallel
+    from irbfn_b200 import ops, parallel, peak
     from irbfn_b200.basis import gaussian
     from irbfn_b200.model import WCRBFNet, device_params
 
@@ -265,9 +265,9 @@ def main():
 
     if rank == 0:
         # ---- roofline of irbfn_fwd_kernel (the only kernel of the step) ----
-        peak_lane, _, _ = ops.fp32_microbench(2, iters=20000)    # FADD2+FFMA2: the distance loop's pair
-        peak_ffma, _, _ = ops.fp32_microbench(0, iters=20000)
-        _, peak_mufu, _ = ops.fp32_microbench(3, iters=5000)
+        peak_lane, _, _ = peak.fp32_microbench(2, iters=20000)    # FADD2+FFMA2: the distance loop's pair
+        peak_ffma, _, _ = peak.fp32_microbench(0, iters=20000)
+        _, peak_mufu, _ = peak.fp32_microbench(3, iters=5000)
         t = ms * 1e-3
         ach_lane = counts["lane_ops"] * B / t
         peaks = {}

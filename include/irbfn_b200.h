@@ -168,18 +168,6 @@ int irbfn_region_gate(const float* x, const IrbfnGateDesc* gd, float* gamma, int
 int irbfn_softmax_gate(const float* x, const float* Wc, const float* bc, float* gate,
                        float* logits, int64_t B, int D, int R, irbfn_stream_t stream);
 
-/* FP32-pipe / XU micro-benchmark used as the roofline denominator (csrc/fp32_peak.cu).
- * scratch: device, blocks*512 floats. */
-int irbfn_fp32_microbench(int mode, int iters, int blocks, float* scratch,
-                          double* fp32_lane_ops_per_s, double* mufu_lane_ops_per_s,
-                          float* elapsed_ms, irbfn_stream_t stream);
-
-/* Same benchmark, all pipes: rates[0] = FP32-pipe, rates[1] = MUFU (XU), rates[2] = FP64-pipe
- * lane-operations per second.  Modes 0-6 as above; 7-56 are the FP32/FP64 co-issue, DMMA and
- * warp-specialisation probes documented at the top of csrc/fp32_peak.cu. */
-int irbfn_pipe_microbench(int mode, int iters, int blocks, float* scratch, double* rates,
-                          float* elapsed_ms, irbfn_stream_t stream);
-
 /* ---------------------------------------------------------------------------------------------
  * Loss-side vehicle dynamics: the tail of the reference's loss_fn after
  * wcrbf.apply, fused into one launch that yields the loss terms AND the cotangent dloss/dy_pred

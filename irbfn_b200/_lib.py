@@ -32,7 +32,7 @@ DYN_FRENET_MULT, DYN_FRENET_ONESTEP_AUX, DYN_ST_MULT, DYN_ST_ONESTEP_AUX = 0, 1,
 EXPORTED_SYMBOLS = (
     "irbfn_abi_version", "irbfn_error_string", "irbfn_last_error_detail", "irbfn_forward_workspace_bytes", "irbfn_forward",
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
-    "irbfn_softmax_gate", "irbfn_fp32_microbench", "irbfn_pipe_microbench", "irbfn_forward_plan",
+    "irbfn_softmax_gate", "irbfn_forward_plan",
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
     "irbfn_gather_rows", "irbfn_grid_index", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
     "irbfn_prediction_loss_workspace_bytes", "irbfn_prediction_loss",
@@ -89,13 +89,8 @@ def load():
     lib.irbfn_region_gate.argtypes = [p, C.POINTER(GateDesc), p, i64, i, i, p]
     lib.irbfn_softmax_gate.restype = i
     lib.irbfn_softmax_gate.argtypes = [p, p, p, p, p, i64, i, i, p]
-    lib.irbfn_fp32_microbench.restype = i
-    lib.irbfn_fp32_microbench.argtypes = [i, i, i, p, C.POINTER(C.c_double),
-                                          C.POINTER(C.c_double), C.POINTER(C.c_float), p]
     lib.irbfn_forward_plan.restype = i
     lib.irbfn_forward_plan.argtypes = [i, i, i, i, i, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(sz)]
-    lib.irbfn_pipe_microbench.restype = i
-    lib.irbfn_pipe_microbench.argtypes = [i, i, i, p, C.POINTER(C.c_double), C.POINTER(C.c_float), p]
     lib.irbfn_dynamics_loss_workspace_bytes.restype = sz
     lib.irbfn_dynamics_loss_workspace_bytes.argtypes = [i64]
     lib.irbfn_prediction_loss_workspace_bytes.restype = sz

@@ -18,6 +18,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_obj")
 LIB = os.path.join(HERE, "libirbfn_b200.so")
+# measurement tooling (FP32 / XU peak probe): its own library, NOT part of the product ABI
+BENCH_CSRC = os.path.join(HERE, "bench_csrc")
+BENCH_LIB = os.path.join(HERE, "libirbfn_bench.so")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -30,8 +33,7 @@ FEATURE_COUNTS = (4, 5, 6, 7, 8)
 
 
 def _units():
-    units = [("irbfn_api.cu", [], "irbfn_api.o"), ("fp32_peak.cu", [], "fp32_peak.o"),
-             ("irbfn_dynamics.cu", [], "irbfn_dynamics.o"),
+    units = [("irbfn_api.cu", [], "irbfn_api.o"), ("irbfn_dynamics.cu", [], "irbfn_dynamics.o"),
              ("irbfn_table.cu", [], "irbfn_table.o"), ("irbfn_optim.cu", [], "irbfn_optim.o")]
     for name in ("irbfn_fwd_inst.cu", "irbfn_bwd_x_inst.cu", "irbfn_bwd_p_inst.cu", "irbfn_jac_inst.cu"):
         if not os.path.exists(os.path.join(CSRC, name)):
@@ -53,7 +55,7 @@ def _nvcc():
 
 def _source_digest():
     h = hashlib.sha256()
-    for root in (CSRC, os.path.join(HERE, "..", "include")):
+    for root in (CSRC, BENCH_CSRC, os.path.join(HERE, "..", "include")):
         for fn in sorted(os.listdir(root)):
             if fn.endswith((".cu", ".cuh", ".h")):
                 with open(os.path.join(root, fn), "rb") as f:
@@ -67,7 +69,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """Build the shared library if sources changed. Returns its path."""
     stamp = os.path.join(OBJ, "digest.txt")
     digest = _source_digest()
-    if not force and os.path.exists(LIB) and os.path.exists(stamp):
+    if not force and os.path.exists(LIB) and os.path.exists(BENCH_LIB) and os.path.exists(stamp):
         with open(stamp) as f:
             if f.read().strip() == digest:
                 return LIB
@@ -92,6 +94,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stderr[-4000:])
+    cmd = [nvcc, *NVCC_FLAGS, "-shared", os.path.join(BENCH_CSRC, "fp32_peak.cu"), "-o", BENCH_LIB]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed for the peak probe:\n" + r.stderr[-4000:])
     with open(stamp, "w") as f:
         f.write(digest)
     if verbose:

@@ -17,7 +17,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
                    GRAD_LOG_SIGS, GRAD_PARAMS, GRAD_X)
 
 __all__ = [
-    "GatePack", "forward", "backward", "region_gate", "softmax_gate", "fp32_microbench", "pipe_microbench",
+    "GatePack", "forward", "backward", "region_gate", "softmax_gate", 
     "dynamics_loss", "integrate", "default_dyn_params", "jacobian",
     "gather_rows", "GridKeys", "grid_index", "nearest_row",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
@@ -233,36 +233,6 @@ def softmax_gate(x, cluster_kernel, cluster_bias, want_logits: bool = True):
                                     _ptr(logits), B, D, R, _stream())
     _lib.check(rc, "irbfn_softmax_gate")
     return gate, logits
-
-
-def fp32_microbench(mode: int, iters: int = 20000, blocks: Optional[int] = None, device=None):
-    """FP32-pipe / XU issue-rate micro-benchmark (csrc/fp32_peak.cu).  Returns
-    (fp32 lane-ops/s, MUFU lane-ops/s, elapsed ms)."""
-    lib = _lib.load()
-    device = torch.device(device if device is not None else "cuda")
-    with torch.cuda.device(device):
-        if blocks is None:
-            blocks = torch.cuda.get_device_properties(device).multi_processor_count * 8
-        scratch = torch.empty(blocks * 512, device=device, dtype=torch.float32)
-        f, m, ms = C.c_double(), C.c_double(), C.c_float()
-        rc = lib.irbfn_fp32_microbench(mode, iters, blocks, _ptr(scratch), C.byref(f), C.byref(m),
-                                       C.byref(ms), _stream())
-    _lib.check(rc, "irbfn_fp32_microbench")
-    return f.value, m.value, ms.value
-
-
-def pipe_microbench(mode: int, iters: int = 20000, blocks: Optional[int] = None, device=None):
-    """All-pipe variant (irbfn_pipe_microbench): (fp32, MUFU, fp64 lane-ops/s, elapsed ms)."""
-    lib = _lib.load()
-    device = torch.device(device if device is not None else "cuda")
-    with torch.cuda.device(device):
-        if blocks is None:
-            blocks = torch.cuda.get_device_properties(device).multi_processor_count * 8
-        scratch = torch.empty(blocks * 512, device=device, dtype=torch.float32)
-        rates, ms = (C.c_double * 3)(), C.c_float()
-        rc = lib.irbfn_pipe_microbench(mode, iters, blocks, _ptr(scratch), rates, C.byref(ms), _stream())
-    _lib.check(rc, "irbfn_pipe_microbench")
-    return rates[0], rates[1], rates[2], ms.value
 
 
 # --------------------------------------------------------------------------- loss-side dynamics

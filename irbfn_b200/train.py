@@ -85,6 +85,72 @@ class TrainState:
     def opt_state(self) -> dict:
         return {"count": self.step, "mu": self.mu, "nu": self.nu}
 
+    # ---- the reference's checkpoint layout -------------------------------------------------------
+    def _tree_of(self, flat: torch.Tensor) -> dict:
+        """A flat buffer laid out like ``self.flat`` -> {'params': {rbf_list: .., linear: ..}} of NumPy copies."""
+        out, off = {}, 0
+        for name, view in self.views.items():
+            m = view.numel()
+            out[name] = flat[off:off + m].view(view.shape).detach().cpu().numpy().copy()
+            off += m
+        p = {"linear": {"bias": out["bias"], "kernel": out["kernel"]}}
+        rb = {k: out[k] for k in ("centers", "log_sigs") if k in out}
+        if rb:
+            p["rbf_list"] = rb
+        return {"params": p}
+
+    def state_dict(self) -> dict:
+        """The tree ``flax.serialization.to_state_dict(TrainState)`` gives for the reference's
+        ``tx = optax.chain(clip_by_global_norm(g), adam(lr))`` (scripts/train_nmpc.py:231-236): what
+        ``checkpoints.save_checkpoint(CKPT_DIR, state, step)`` writes (:497-502) and
+        ``restore_checkpoint(ckpt_dir, target=state)`` expects (irbfn_planner.py:88-90):
+
+            {step, params: {params: tree},
+             opt_state: {'0': {},                                   # clip_by_global_norm: EmptyState
+                         '1': {'0': {count, mu: {params: tree}, nu: {params: tree}},   # scale_by_adam
+                               '1': {}}}}                           # scale(-lr): EmptyState
+
+        Pass it to ``checkpoint.save_checkpoint``."""
+        return {"step": np.int64(self.step),
+                "params": self._tree_of(self.flat),
+                "opt_state": {"0": {}, "1": {"0": {"count": np.int32(self.step), "mu": self._tree_of(self.mu),
+                                                   "nu": self._tree_of(self.nu)}, "1": {}}}}
+
+    def load_state_dict(self, tree: dict) -> "TrainState":
+        """Resume from a checkpoint tree in the reference's layout (``checkpoint.load_checkpoint``): parameters,
+        both Adam moments and the step count.  Also accepts the bare-Adam layout of the oldest shipped
+        checkpoints (``opt_state['0'] = {count, mu, nu}``, e.g. scripts/ckpts/nmpc_4_regions)."""
+        def fill(flat, sub):
+            p = sub["params"] if "params" in sub else sub
+            src = {"centers": p.get("rbf_list", {}).get("centers"), "log_sigs": p.get("rbf_list", {}).get("log_sigs"),
+                   "kernel": p["linear"]["kernel"], "bias": p["linear"]["bias"]}
+            off = 0
+            for name, view in self.views.items():
+                if src[name] is None:
+                    raise KeyError("checkpoint has no leaf for '%s'" % name)
+                leaf = _leaf(src[name], self.device)
+                if tuple(leaf.shape) != tuple(view.shape):
+                    raise ValueError("leaf '%s': checkpoint %s, module %s" % (name, tuple(leaf.shape), tuple(view.shape)))
+                flat[off:off + view.numel()].copy_(leaf.reshape(-1))
+                off += view.numel()
+
+        fill(self.flat, tree["params"])
+        opt = tree.get("opt_state") or {}
+        adam = None
+        for node in (opt.get("1", {}).get("0") if isinstance(opt.get("1"), dict) else None, opt.get("0"), opt):
+            if isinstance(node, dict) and "mu" in node and "nu" in node:
+                adam = node
+                break
+        if adam is not None:
+            fill(self.mu, adam["mu"])
+            fill(self.nu, adam["nu"])
+            self.step = int(np.asarray(adam.get("count", tree.get("step", 0))))
+        else:
+            self.mu.zero_(); self.nu.zero_()
+            self.step = int(np.asarray(tree.get("step", 0)))
+        self.step_t.fill_(float(self.step))
+        return self
+
 
 def _leaf_device(p):
     for v in p.values():

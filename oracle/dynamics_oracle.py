@@ -2,9 +2,11 @@
 losses.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg
 may import this; the product (irbfn_b200/) never does.
 
-Parity unpinned: the reference has no tests or golden vectors for these functions and JAX cannot be
-imported here, so this file restates the source line by line (torch CPU, float64 by default) and
-gets gradients from torch autograd -- an independent check of the hand-derived adjoints in
+Parity pinned by executing the reference: src/irbfn_mpc/dynamics.py and the nested train_step_*
+functions of scripts/train_nmpc.py / scripts/train_nmpc_frenet.py are run UNMODIFIED under oracle/refshim
+(tests/golden/make_golden.py -> tests/golden/dynamics_ref.npz, train_step_ref.npz); this restatement
+(torch CPU, float64 by default, gradients from torch autograd) reproduces those values to 1e-12
+(tests/test_oracle_vs_ref.py) and is the independent check of the hand-derived adjoints in
 irbfn_b200/csrc/irbfn_dynamics.cu.
 
 Restated (paths relative to the reference checkout):

@@ -5,12 +5,14 @@ evaluation.  Only ``tests/``, ``__graft_entry__.smoke()`` and the
 ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may import it.
 The product path (``irbfn_b200``) never does.
 
-PARITY UNPINNED: the reference ships no golden vectors or known-answer tests
-for this path and JAX/Flax/flax_rbf are not installable in
-this environment, so the oracle is pinned only by (a) following the reference
-source line by line, (b) the survey's independent spot value for
-``nmpc_4_regions/checkpoint_0`` (tests/test_oracle.py) and (c) a literal
-torch-autograd restatement used as an independent gradient check.
+PARITY PINNED BY EXECUTING THE REFERENCE: the reference ships no golden vectors or known-answer
+tests for this path and JAX/Flax/flax_rbf are not installable here, so the
+reference's own source files (src/irbfn_mpc/model.py, the flax_rbf snapshot) are imported UNMODIFIED
+under the torch-CPU library stand-ins of ``oracle/refshim`` and run on the shipped checkpoints
+(tests/golden/make_golden.py).  Every committed fixture value is what that code returned; this oracle
+reproduces all of them to 1e-12 (outputs) / 1e-9 (gradients) -- tests/test_oracle_vs_ref.py, which also
+re-executes the reference live wherever /root/reference exists.  Gradients are autodiff of the
+reference's executed forward (the reference has no gradient code of its own, F7).
 
 Reference lines followed (paths relative to the reference checkout):
   gate      : src/irbfn_mpc/model.py:70-95   (_region_activation)

@@ -24,7 +24,9 @@ def pytest_configure(config):
 
 
 def golden_paths():
-    return sorted(glob.glob(os.path.join(GOLDEN_DIR, "*.npz")))
+    """Model fixtures (one per shipped checkpoint).  ``*_ref.npz`` are the dynamics / training-step
+    fixtures, which have their own layout."""
+    return sorted(p for p in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")) if not p.endswith("_ref.npz"))
 
 
 def load_golden(path):

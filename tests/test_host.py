@@ -96,3 +96,75 @@ def test_stress_shape_is_chunked_within_shared_memory():
     assert _plan(3520, 100, 4, 5)[0] == 0                   # the IROS-2023 many-region shape
     assert _plan(12, 100, 8, 2, smem=2048)[0] != 0          # impossible budget -> error code, no crash
     assert _plan(12, 100, 9, 2)[0] == -2                    # D > IRBFN_MAX_D
+
+
+# ---- reference-held checkpoint data (tests/golden/make_golden.py: make_checkpoint_fixture) -----------------
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_reader_decodes_real_flax_checkpoint_bytes():
+    """irbfn_b200/checkpoint.py on the raw bytes of a checkpoint the REFERENCE wrote
+    (scripts/ckpts/nmpc_4_regions/checkpoint_0), leaf by leaf against the fixture parameters that
+    tests/golden/make_golden.py decoded with the oracle's separate reader."""
+    raw = checkpoint.load_checkpoint(os.path.join(GOLDEN, "ref_ckpt_nmpc_4_regions_checkpoint_0.msgpack"))
+    assert set(raw) == {"step", "params", "opt_state"} and int(raw["step"]) == 5184000
+    p = raw["params"]["params"]
+    assert p["rbf_list"]["centers"].dtype == np.float64 and p["linear"]["kernel"].dtype == np.float32   # F6
+    z = np.load(os.path.join(GOLDEN, "c1b_nmpc_4_regions.npz"))
+    restored = checkpoint.restore_params(os.path.join(GOLDEN, "ref_ckpt_nmpc_4_regions_checkpoint_0.msgpack"))["params"]
+    for path in ("rbf_list/centers", "rbf_list/log_sigs", "linear/kernel", "linear/bias"):
+        a, b = path.split("/")
+        assert restored[a][b].dtype == np.float32
+        assert np.array_equal(restored[a][b], z["p/" + path]), path
+        assert np.array_equal(p[a][b].astype(np.float32), z["p/" + path]), path
+
+
+def _layout(node):
+    if isinstance(node, dict):
+        return {str(k): _layout(v) for k, v in node.items()}
+    a = np.asarray(node)
+    return [list(a.shape), a.dtype.name]
+
+
+def test_train_state_writes_and_resumes_the_reference_checkpoint_layout(tmp_path):
+    """TrainState.state_dict() has the key / shape structure of a checkpoint the reference wrote with
+    optax.chain(clip_by_global_norm, adam) (layout recorded from scripts/ckpts/dnmpc_12regions_frenet_l1_bigdata/
+    checkpoint_9500), survives the msgpack codec, and load_state_dict() resumes params, moments and count."""
+    import json
+    import torch
+    from irbfn_b200.train import TrainState
+    with open(os.path.join(GOLDEN, "ckpt_layouts.json")) as f:
+        layouts = json.load(f)
+    want = layouts["scripts/ckpts/dnmpc_12regions_frenet_l1_bigdata/checkpoint_9500"]
+    z = np.load(os.path.join(GOLDEN, "c2_frenet_12x100.npz"))
+    cfg = json.loads(str(z["cfg_json"]))
+    net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], basis.gaussian, cfg["num_regions"],
+                   cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"], cfg["delta"])
+    tree = {"params": {"rbf_list": {"centers": z["p/rbf_list/centers"], "log_sigs": z["p/rbf_list/log_sigs"]},
+                       "linear": {"kernel": z["p/linear/kernel"], "bias": z["p/linear/bias"]}}}
+    st = TrainState(net, tree, lr=1e-3, device="cpu")
+    st.mu.copy_(torch.arange(st.mu.numel()) * 1e-3)
+    st.nu.copy_(torch.arange(st.nu.numel()) * 2e-3)
+    st.step = 41
+    sd = st.state_dict()
+
+    def shapes_only(n):
+        return {k: shapes_only(v) for k, v in n.items()} if isinstance(n, dict) else n[0]
+    assert shapes_only(_layout(sd)) == shapes_only(want)                 # same keys, nesting and shapes
+    assert _layout(sd)["opt_state"]["1"]["0"]["count"] == want["opt_state"]["1"]["0"]["count"]   # int32 scalar
+    path = checkpoint.save_checkpoint(str(tmp_path), sd, step=41)
+    back = checkpoint.load_checkpoint(path)
+    assert shapes_only(_layout(back)) == shapes_only(want)
+    st2 = TrainState(net, tree, lr=1e-3, device="cpu")
+    st2.flat.zero_()
+    st2.load_state_dict(back)
+    assert st2.step == 41 and float(st2.step_t) == 41.0
+    assert torch.equal(st2.flat, st.flat) and torch.equal(st2.mu, st.mu) and torch.equal(st2.nu, st.nu)
+    # the oldest shipped checkpoints hold a bare Adam state (opt_state['0'] = {count, mu, nu}): resumable too
+    old = checkpoint.load_checkpoint(os.path.join(GOLDEN, "ref_ckpt_nmpc_4_regions_checkpoint_0.msgpack"))
+    z4 = np.load(os.path.join(GOLDEN, "c1b_nmpc_4_regions.npz"))
+    c4 = json.loads(str(z4["cfg_json"]))
+    net4 = WCRBFNet(c4["in_features"], c4["out_features"], c4["num_kernels"], basis.inverse_quadratic, c4["num_regions"],
+                    c4["lower_bounds"], c4["upper_bounds"], c4["dimension_ranges"], c4["activation_idx"], c4["delta"])
+    st4 = TrainState(net4, old["params"], lr=1e-3, device="cpu").load_state_dict(old)
+    assert st4.step == int(old["opt_state"]["0"]["count"]) and np.array_equal(st4.views["kernel"].numpy(), z4["p/linear/kernel"])

@@ -1,10 +1,8 @@
 """CPU tests of the oracle (oracle/irbfn_oracle.py) against the committed golden fixtures.
 
-The fixtures were generated from the reference's shipped checkpoints + configs by
-tests/golden/make_golden.py and cross-checked there against a literal torch-float64
-transcription of the reference forward differentiated by autograd.  The reference ships no
-known-answer tests for this path, so the pins are: the fixtures, the
-survey's independent spot value, and the literal restatement below.
+The fixtures hold values produced by the reference's own source executed under oracle/refshim
+(tests/golden/make_golden.py; tests/test_oracle_vs_ref.py is the pin itself).  Kept here: the survey's
+independent spot value, the fp32-vs-fp64 margin, and a literal torch restatement as a third opinion.
 """
 import numpy as np
 import pytest
