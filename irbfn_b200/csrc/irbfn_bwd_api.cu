@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include "irbfn_bwd_p.cuh"
+#include "irbfn_bwd_pw.cuh"
 #include "irbfn_bwd_x.cuh"
 #include "irbfn_common.cuh"
 #include "irbfn_plan.h"
@@ -13,6 +14,11 @@ int launch_bwd_p_d5(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream
 int launch_bwd_p_d6(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_p_d7(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_p_d8(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_pw_d4(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_pw_d5(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_pw_d6(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_pw_d7(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_pw_d8(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_x_d4(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
 int launch_bwd_x_d5(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
 int launch_bwd_x_d6(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
@@ -255,6 +261,10 @@ static bool bwd_layout(int64_t B, int R, int K, int D, int O, unsigned mask, int
             if (!plan_bwd_p(B, R, K, DT, D, O, fwd_ot_for(ocur), has_dhid, sms, smem, &pp)) return false;
             if (o0 == 0) L->pplan = pp;
             if (pp.part_floats > max_part) max_part = pp.part_floats;
+            BwdPWPlan pw;   // the region-lane kernel may take this window instead: size for either
+            if (bwdpw_applies(R, O, has_dhid) && plan_bwd_pw(B, R, K, DT, O, fwd_ot_for(ocur), sms, smem, &pw) &&
+                pw.part_floats > max_part)
+                max_part = pw.part_floats;
             if (pp.splits > max_splits) max_splits = pp.splits;
             o0 += ocur;
         } while (o0 < O);
@@ -349,6 +359,32 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             const int ocur = Oeff - o0 > 16 ? 16 : Oeff - o0;
             const int OT = fwd_ot_for(ocur);
             BwdPPlan pp;
+            BwdPWPlan pw;
+            const bool wide = bwdpw_applies(R, Oeff, dhidden != nullptr) && plan_bwd_pw(B, R, K, DT, Oeff, OT, sms, smem, &pw);
+            if (wide) {
+                // several regions share a wide readout: lanes = regions, dh from a per-tile table, dW from the
+                // region-summed activation (irbfn_bwd_pw.cuh)
+                if (pw.part_floats > L.max_part_floats) return IRBFN_ERR_WORKSPACE;
+                if ((long long)R * pw.splits >= (1ll << 31)) return IRBFN_ERR_BAD_DIMS;
+                BwdPWArgs w{};
+                w.x = x; w.centers = centers; w.log_sigs = log_sigs; w.W = W; w.gate = gate_p; w.dy = dy;
+                w.part = (float*)(ws + L.part_off);
+                w.B = B; w.R = R; w.K = K; w.Dsrc = D; w.O = Oeff;
+                w.G = pw.G; w.NRG = pw.NRG; w.units = pw.units; w.units_per_cta = pw.units_per_cta;
+                w.nchunks = pw.nchunks; w.splits = pw.splits; w.TQ = pw.TQ; w.Kspan = pw.Kspan;
+                const int grid = pw.nchunks * pw.splits;
+                int e;
+                switch (DT) {
+                    case 4: e = launch_bwd_pw_d4(w, OT, basis, grid, pw.NT, pw.smem_bytes, st); break;
+                    case 5: e = launch_bwd_pw_d5(w, OT, basis, grid, pw.NT, pw.smem_bytes, st); break;
+                    case 6: e = launch_bwd_pw_d6(w, OT, basis, grid, pw.NT, pw.smem_bytes, st); break;
+                    case 7: e = launch_bwd_pw_d7(w, OT, basis, grid, pw.NT, pw.smem_bytes, st); break;
+                    default: e = launch_bwd_pw_d8(w, OT, basis, grid, pw.NT, pw.smem_bytes, st); break;
+                }
+                if (e != 0) return note_cuda_error("irbfn_bwd_pw_kernel", e);
+                pp = BwdPPlan{};
+                pp.splits = pw.splits; pp.PW = pw.PW;
+            } else {
             if (!plan_bwd_p(B, R, K, DT, D, Oeff, OT, dhidden != nullptr, sms, smem, &pp)) return IRBFN_ERR_BAD_DIMS;
             if (pp.part_floats > L.max_part_floats) return IRBFN_ERR_WORKSPACE;
             if ((long long)R * pp.splits >= (1ll << 31)) return IRBFN_ERR_BAD_DIMS;   // reduce_p_kernel's term index
@@ -370,8 +406,9 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
                 default: e = launch_bwd_p_d8(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
             }
             if (e != 0) return note_cuda_error("irbfn_bwd_p_kernel", e);
+            }
             ReduceArgs r{};
-            r.part = a.part; r.part_db = (float*)(ws + L.partdb_off); r.log_sigs = log_sigs;
+            r.part = (float*)(ws + L.part_off); r.part_db = (float*)(ws + L.partdb_off); r.log_sigs = log_sigs;
             r.dC = (first && (grad_mask & IRBFN_GRAD_CENTERS)) ? dcenters : nullptr;
             r.dLS = (first && (grad_mask & IRBFN_GRAD_LOG_SIGS)) ? dlog_sigs : nullptr;
             r.dW = ((grad_mask & IRBFN_GRAD_KERNEL) && ocur > 0) ? dW : nullptr;

@@ -231,4 +231,83 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     return true;
 }
 
+// ---------------------------------------------------------------------------------------
+// backward P, wide outputs over several regions (irbfn_bwd_pw.cuh): lanes = regions of a kernel pair.
+// Chosen when the readout is wide enough (O > 4) for the per-(region, kernel) dh / dW work of the
+// thread-private kernel to dominate, several regions share the readout (R >= 2), one output window
+// suffices (O <= 16) and the cotangent is dy (no dhidden).
+// ---------------------------------------------------------------------------------------
+constexpr int kPwNQ_h = 16;              // must match kPwNQ / kPwLS in irbfn_bwd_pw.cuh
+constexpr int kPwLS_h = 2 * kPwNQ_h + 2;
+
+struct BwdPWPlan {
+    int OT, NT;
+    int G, NRG, units, units_per_cta, nchunks, splits;
+    int TQ, Kspan, PW;
+    size_t smem_bytes;
+    size_t part_floats;
+};
+
+inline bool bwdpw_applies(int R, int O, int has_dhid) { return R >= 2 && O > 4 && O <= 16 && !has_dhid; }
+
+inline size_t bwdpw_smem_floats(int TQ, int D, int O, int OT, int Kspan, int NW) {
+    (void)O;
+    const int WS = ((OT + 3) / 4) * 4, DS = WS + (WS % 8 == 0 ? 4 : 0);   // must match irbfn_bwd_pw.cuh
+    size_t st = (size_t)TQ * bwdp_xs_h(D) + (size_t)TQ * DS;
+    st = ((st + 3) / 4) * 4;
+    return 2 * st + (size_t)TQ * Kspan + (size_t)Kspan * WS + (size_t)NW * 32 * kPwLS_h;
+}
+
+inline bool plan_bwd_pw(long long B, int R, int K, int D, int O, int OT, int sms, int smem_limit, BwdPWPlan* p) {
+    if (!bwdpw_applies(R, O, 0) || OT < O || (long long)R * K > (1ll << 30)) return false;
+    int G = 32;
+    if (R < 32) { G = 2; while (G < R) G <<= 1; }
+    const int NRG = (R + G - 1) / G;
+    const int KP = (K + 1) / 2;
+    const long long units_ll = (long long)KP * NRG;
+    if (units_ll > (1ll << 30)) return false;
+    const int units = (int)units_ll;
+    const int upw = 32 / G;                                  // units per warp
+    const int max_warps = (OT <= 10 && D <= 7) ? 16 : 12;    // register budget: 128 / 168 per thread (irbfn_bwd_pw.cuh)
+    const int per_cta = max_warps * upw;
+    const int nchunks = (units + per_cta - 1) / per_cta;
+    const int upc = (units + nchunks - 1) / nchunks;         // units per CTA
+    int NW = (((upc + upw - 1) / upw + 3) / 4) * 4;          // a multiple of four warps: one per SM sub-partition
+    if (NW > max_warps) NW = max_warps;
+    // kernel pairs one CTA can touch: its units span at most ceil(upc / NRG) + 1 pairs
+    int Kspan = 2 * ((upc + NRG - 1) / NRG + (NRG > 1 ? 1 : 0));
+    if (Kspan > 2 * KP) Kspan = 2 * KP;
+    int TQ = 256;
+    while (TQ >= kPwNQ_h && bwdpw_smem_floats(TQ, D, O, OT, Kspan, NW) * sizeof(float) > (size_t)smem_limit) TQ -= kPwNQ_h;
+    if (TQ < kPwNQ_h) return false;
+    // splits: fill the device, and prefer a grid close to a whole number of waves
+    long long splits = nchunks <= sms ? sms / nchunks : (4ll * sms + nchunks - 1) / nchunks;
+    if (splits < 1) splits = 1;
+    if (nchunks > sms) {
+        double best = 0.0;
+        long long best_s = splits;
+        for (long long s = splits; s <= splits + 6; ++s) {
+            const long long grid = s * nchunks, waves = (grid + sms - 1) / sms;
+            const double eff = (double)grid / (double)(waves * sms);
+            if (eff > best + 1e-9) { best = eff; best_s = s; }
+        }
+        splits = best_s;
+    }
+    if (B > 0) {
+        const long long m = (B + splits * TQ - 1) / (splits * TQ);
+        long long tqb = (B + splits * m - 1) / (splits * m);
+        tqb = ((tqb + kPwNQ_h - 1) / kPwNQ_h) * kPwNQ_h;
+        if (tqb < TQ) TQ = (int)tqb;
+    }
+    const long long ntiles = (B + TQ - 1) / TQ;
+    if (splits > ntiles) splits = ntiles;
+    if (splits < 1) splits = 1;
+    p->OT = OT; p->NT = NW * 32;
+    p->G = G; p->NRG = NRG; p->units = units; p->units_per_cta = upc; p->nchunks = nchunks; p->splits = (int)splits;
+    p->TQ = TQ; p->Kspan = Kspan; p->PW = D + 1 + OT;
+    p->smem_bytes = bwdpw_smem_floats(TQ, D, O, OT, Kspan, NW) * sizeof(float);
+    p->part_floats = (size_t)splits * (size_t)R * (size_t)K * (size_t)p->PW;
+    return true;
+}
+
 }  // namespace irbfn

@@ -127,6 +127,35 @@ def test_backward_parameters_larger_than_shared_memory(cuda_device):
         assert rel_l2(g[name].cpu().numpy(), ref[name]) < GRAD_TOL, name
 
 
+WIDE_SHAPES = [
+    # B, R, K, D, O : several regions under a wide readout -> irbfn_bwd_pw_kernel (lanes = regions).
+    # group sizes 2..32, ragged last region group, odd K, O below / at the window, ragged query tiles
+    (777, 40, 11, 6, 16), (4099, 17, 7, 8, 12), (333, 64, 20, 6, 16), (1500, 27, 50, 8, 10), (513, 9, 101, 7, 6),
+    (2000, 5, 64, 5, 8), (90, 33, 3, 4, 5), (17, 2, 1, 8, 16),
+]
+
+
+@pytest.mark.parametrize("shape", WIDE_SHAPES, ids=["B%d_R%d_K%d_D%d_O%d" % s for s in WIDE_SHAPES])
+def test_wide_readout_parameter_gradients(shape, cuda_device):
+    ops = _ops()
+    B, R, K, D, O = shape
+    cfg, p, x = _synthetic(29, B, R, K, D, O, S=min(3, D), nb=(4, 3, 3))
+    dev = cuda_device
+    dy = np.random.default_rng(4).normal(size=(B, O)).astype(np.float32)
+    params = {"rbf_list": {"centers": p["centers"], "log_sigs": p["log_sigs"]},
+              "linear": {"kernel": p["kernel"], "bias": p["bias"]}}
+    for basis in (0, 1):
+        cfg["basis_func"] = "gaussian" if basis == 0 else "inverse_quadratic"
+        ref = orc.wcrbf_vjp(x.astype(np.float64), params, cfg, dy.astype(np.float64), chunk=64)
+        args = (_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev), _t(dy, dev))
+        g = ops.backward(*args, gd=_gd(cfg, dev), basis=basis, grad_mask=ops.GRAD_PARAMS)
+        for name in ("centers", "log_sigs", "kernel", "bias"):
+            assert rel_l2(g[name].cpu().numpy(), ref[name]) < GRAD_TOL, (name, basis)
+        g2 = ops.backward(*args, gd=_gd(cfg, dev), basis=basis, grad_mask=ops.GRAD_PARAMS)
+        for name in ("centers", "log_sigs", "kernel", "bias"):
+            assert torch.equal(g[name], g2[name]), "not deterministic: %s" % name
+
+
 def test_query_on_centre_gives_finite_analytic_limit(cuda_device):
     """F8: the reference's sqrt form gives NaN here; the kernels work on d^2."""
     ops = _ops()
