@@ -125,6 +125,8 @@ __global__ void __launch_bounds__((OT <= 10 && D <= 7) ? 512 : 384, 1) irbfn_bwd
     const int rd_src = g * G + (G >= NQ ? (rr / NQ) * NQ : 0);
     const int rd_q0 = G >= NQ ? rr % NQ : rr;
 
+    const long long gpitch = (long long)a.R * (long long)sizeof(float);   // bytes between gate rows
+    const int dhpitch2 = 2 * Kspan;                                       // floats between dh rows two queries apart
     const long long ntiles = (a.B + TQ - 1) / TQ;
     auto issue_tile = [&](long long tile, int stage) {
         float* sb = smem + (size_t)stage * stage_floats;
@@ -182,63 +184,105 @@ __global__ void __launch_bounds__((OT <= 10 && D <= 7) ? 512 : 384, 1) irbfn_bwd
         __syncthreads();
 
         // gamma of (query, this lane's region): a ring of four loads in flight, four queries ahead of use
-        const float* gbase = a.gate + q0 * a.R + (lane_ok ? r : 0);
-        unsigned goff = 0;                                   // float offset of the next row to load (< 2^31: TQ * R)
+        // (a per-lane pointer bumped by the row pitch: two integer instructions per load)
+        const char* gptr = reinterpret_cast<const char*>(a.gate + q0 * a.R + (lane_ok ? r : 0));
         float gr[4];
 #pragma unroll
-        for (int t = 0; t < 4; ++t) { gr[t] = (lane_ok && t < tq) ? __ldg(gbase + goff) : 0.f; goff += a.R; }
-        // x row and dh pair of the next query, one query ahead (row TQ of either table is finite padding)
-        float4 xn[XS / 4];
-#pragma unroll
-        for (int t = 0; t < XS / 4; ++t) xn[t] = reinterpret_cast<const float4*>(sb + st_x)[t];
+        for (int t = 0; t < 4; ++t) {
+            gr[t] = (lane_ok && t < tq) ? __ldg(reinterpret_cast<const float*>(gptr)) : 0.f;
+            gptr += gpitch;
+        }
+        // x rows and dh pairs of the next TWO queries, loaded while the current two are computed (row TQ and
+        // TQ + 1 of either table are finite padding)
+        float4 xn[2][XS / 4];
+        float2 dhn[2];
         const float* dhp = dhs + kk;
-        float2 dhn = *reinterpret_cast<const float2*>(dhp);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+#pragma unroll
+            for (int t = 0; t < XS / 4; ++t) xn[u][t] = reinterpret_cast<const float4*>(sb + st_x + u * XS)[t];
+            dhn[u] = *reinterpret_cast<const float2*>(dhp + u * Kspan);
+        }
 
-        // one batch of 16 queries: thread-private centre / width gradients, v = gamma * phi to the scratch.
-        // FAST: every lane of the warp owns a region and the ring's loads stay inside the tile -> no predicates.
+        // one batch of 16 queries, two at a time with their instructions interleaved (two independent
+        // dependency chains per warp: with three warps per scheduler a single chain leaves the FP32 pipe
+        // waiting on its own 4-cycle latencies): thread-private centre / width gradients, v = gamma * phi to
+        // the scratch.  FAST: every lane of the warp owns a region and the ring's loads stay inside the tile.
         auto batch = [&](int qb, auto fast_tag) {
             constexpr bool FAST = decltype(fast_tag)::value;
             const float* xb = sb + st_x + (size_t)qb * XS;
             float* sw = scr + lane * LS;
 #pragma unroll
-            for (int i = 0; i < NQ; ++i) {
-                const float gq = gr[i & 3];
-                if (FAST) gr[i & 3] = __ldg(gbase + goff);
-                else gr[i & 3] = (lane_ok && qb + i + 4 < tq) ? __ldg(gbase + goff) : 0.f;
-                goff += a.R;
-                float xv[XS];
+            for (int i = 0; i < NQ; i += 2) {
+                float gq[2], xv[2][XS];
+                float2 dh2[2];
 #pragma unroll
-                for (int t = 0; t < XS / 4; ++t) {
-                    xv[4 * t] = xn[t].x; xv[4 * t + 1] = xn[t].y; xv[4 * t + 2] = xn[t].z; xv[4 * t + 3] = xn[t].w;
+                for (int u = 0; u < 2; ++u) {
+                    gq[u] = gr[(i + u) & 3];
+                    if (FAST) gr[(i + u) & 3] = __ldg(reinterpret_cast<const float*>(gptr));
+                    else gr[(i + u) & 3] = (lane_ok && qb + i + u + 4 < tq) ? __ldg(reinterpret_cast<const float*>(gptr)) : 0.f;
+                    gptr += gpitch;
+#pragma unroll
+                    for (int t = 0; t < XS / 4; ++t) {
+                        xv[u][4 * t] = xn[u][t].x; xv[u][4 * t + 1] = xn[u][t].y;
+                        xv[u][4 * t + 2] = xn[u][t].z; xv[u][4 * t + 3] = xn[u][t].w;
+                    }
+                    dh2[u] = dhn[u];
                 }
-                const float2 dh2 = dhn;
+                dhp += dhpitch2;
 #pragma unroll
-                for (int t = 0; t < XS / 4; ++t) xn[t] = reinterpret_cast<const float4*>(xb + (i + 1) * XS)[t];
-                dhp += Kspan;
-                dhn = *reinterpret_cast<const float2*>(dhp);
-                float2 df[D];
-                df[0] = add2(nc2[0], dup2(xv[0]));
-                float2 d2 = mul2(df[0], df[0]);
+                for (int u = 0; u < 2; ++u) {
 #pragma unroll
-                for (int j = 1; j < D; ++j) {
-                    df[j] = add2(nc2[j], dup2(xv[j]));
-                    d2 = fma2(df[j], df[j], d2);
+                    for (int t = 0; t < XS / 4; ++t) xn[u][t] = reinterpret_cast<const float4*>(xb + (i + 2 + u) * XS)[t];
                 }
-                float2 phi;
-                if (BASIS == IRBFN_BASIS_GAUSSIAN) {
-                    const float2 e = mul2(d2, sc2);
-                    phi = make_float2(ex2_approx(e.x), ex2_approx(e.y));
-                } else {
-                    const float2 e = fma2(d2, sc2, make_float2(1.f, 1.f));
-                    phi = make_float2(rcp_approx(e.x), rcp_approx(e.y));
-                }
-                const float2 v = mul2(dup2(gq), phi);        // gamma * phi (0 beyond the tile: gamma = 0)
-                *reinterpret_cast<float2*>(sw + 2 * i) = v;
-                float2 t = mul2(v, dh2);
-                if (BASIS == IRBFN_BASIS_INVERSE_QUADRATIC) t = mul2(t, phi);
+                dhn[0] = *reinterpret_cast<const float2*>(dhp);
+                dhn[1] = *reinterpret_cast<const float2*>(dhp + Kspan);
+                float2 df[2][D], d2[2], d2b[2];
 #pragma unroll
-                for (int j = 0; j < D; ++j) aC[j] = fma2(t, df[j], aC[j]);
-                aL = fma2(t, d2, aL);
+                for (int u = 0; u < 2; ++u) {
+                    df[u][0] = add2(nc2[0], dup2(xv[u][0]));
+                    d2[u] = mul2(df[u][0], df[u][0]);
+                    if (D > 1) {
+                        df[u][1] = add2(nc2[1], dup2(xv[u][1]));
+                        d2b[u] = mul2(df[u][1], df[u][1]);
+                    }
+                }
+#pragma unroll
+                for (int j = 2; j < D; ++j) {
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        df[u][j] = add2(nc2[j], dup2(xv[u][j]));
+                        if (j & 1) d2b[u] = fma2(df[u][j], df[u][j], d2b[u]);
+                        else d2[u] = fma2(df[u][j], df[u][j], d2[u]);
+                    }
+                }
+                float2 phi[2], v[2], t[2];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    if (D > 1) d2[u] = add2(d2[u], d2b[u]);
+                    if (BASIS == IRBFN_BASIS_GAUSSIAN) {
+                        const float2 e = mul2(d2[u], sc2);
+                        phi[u] = make_float2(ex2_approx(e.x), ex2_approx(e.y));
+                    } else {
+                        const float2 e = fma2(d2[u], sc2, make_float2(1.f, 1.f));
+                        phi[u] = make_float2(rcp_approx(e.x), rcp_approx(e.y));
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    v[u] = mul2(dup2(gq[u]), phi[u]);            // gamma * phi (0 beyond the tile: gamma = 0)
+                    t[u] = mul2(v[u], dh2[u]);
+                    if (BASIS == IRBFN_BASIS_INVERSE_QUADRATIC) t[u] = mul2(t[u], phi[u]);
+                }
+                *reinterpret_cast<float2*>(sw + 2 * i) = v[0];
+                *reinterpret_cast<float2*>(sw + 2 * i + 2) = v[1];
+#pragma unroll
+                for (int j = 0; j < D; ++j) {
+                    aC[j] = fma2(t[0], df[0][j], aC[j]);
+                    aC[j] = fma2(t[1], df[1][j], aC[j]);
+                }
+                aL = fma2(t[0], d2[0], aL);
+                aL = fma2(t[1], d2[1], aL);
             }
         };
 
@@ -252,8 +296,18 @@ __global__ void __launch_bounds__((OT <= 10 && D <= 7) ? 512 : 384, 1) irbfn_bwd
                 const int qi = rd_q0 + f * G;                 // query within the batch (f == 0 when G >= NQ)
                 const float* sp = scr + (size_t)rd_src * LS + 2 * qi;
                 float2 h = make_float2(0.f, 0.f);
+                if (rd_per == NQ) {                            // G >= 16: always 16 source lanes, fully unrolled
+                    float2 h1 = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int s = 0; s < NQ; s += 2) {
+                        h = add2(h, *reinterpret_cast<const float2*>(sp + s * LS));
+                        h1 = add2(h1, *reinterpret_cast<const float2*>(sp + (s + 1) * LS));
+                    }
+                    h = add2(h, h1);
+                } else {
 #pragma unroll 4
-                for (int s = 0; s < rd_per; ++s) h = add2(h, *reinterpret_cast<const float2*>(sp + (size_t)s * LS));
+                    for (int s = 0; s < rd_per; ++s) h = add2(h, *reinterpret_cast<const float2*>(sp + (size_t)s * LS));
+                }
                 const float* dp = sb + st_dy + (size_t)(qb + qi) * DS;
                 float dyv[DS];
 #pragma unroll
