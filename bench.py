@@ -40,6 +40,7 @@ sys.path.insert(0, ROOT)
 FIXTURE = os.path.join(ROOT, "tests", "golden", "c2_frenet_12x100.npz")
 LATTICE = (("ey", 0, 32), ("epsi", 6, 32), ("vx_car", 2, 16), ("wz", 5, 8), ("delta", 1, 4), ("vy_car", 3, 2))
 B_LATTICE = 1 << 20
+CPU_SAMPLE = 1 << 18      # stride sample of the lattice both CPU legs (cpu_baseline, --impl reference) time
 METRIC = "irbfn_forward_queries_per_s"
 UNIT = "queries/s"
 
@@ -157,7 +158,7 @@ def run_reference(args):
         return
     from oracle import c_oracle
     cfg, p = load_c2()
-    sample = 1 << 17
+    sample = CPU_SAMPLE
     x = lattice(cfg)[:: B_LATTICE // sample].copy()
     # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every core this process may run on
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
@@ -291,12 +292,13 @@ def main():
                     "peak_source": "measured" if "hbm_gbs" in peaks else "fallback"},
         }
 
+        tail = {}
         if not args.no_extras:
-            out["extras"] = extras(net, params, cfg, dev, world, args)
+            out["extras"], tail = extras(net, params, cfg, dev, world, args)
 
         if world == 1 and not args.no_cpu:
             from oracle import c_oracle
-            sample = 1 << 18
+            sample = CPU_SAMPLE
             xs_cpu = xs[0][:: B // sample].cpu().numpy().copy()
             cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
             run = lambda: c_oracle.forward(xs_cpu, p_np["rbf_list"]["centers"], p_np["rbf_list"]["log_sigs"],
@@ -314,6 +316,7 @@ def main():
                                              "oracle/irbfn_oracle.c (float32, OpenMP)" % (sample, reps)}
             out["parity_check"] = {"max_abs_err_over_max_abs": float(np.abs(y_gpu - y_cpu).max() / np.abs(y_cpu).max()),
                                    "against": "C oracle float32, same %d queries" % sample}
+        out.update(tail)      # compact c3 / c5 / dp_parity objects LAST: they survive a truncated tail of the line
         emit(out)
     elif not args.no_extras:
         extras(net, params, cfg, dev, world, args)   # collectives inside: every rank takes part
@@ -329,7 +332,7 @@ def extras(net, params, cfg, dev, world, args):
     from irbfn_b200 import ops, parallel
     from irbfn_b200.train import TrainState, grad_step, train_step
     rank = parallel.env_world()[0]
-    res = {}
+    res, tail = {}, {}
     p = params["params"]
     R, K, D, O = cfg["num_regions"], cfg["num_kernels"], cfg["in_features"], cfg["out_features"]
     lo = np.array([min(b) for b in cfg["lower_bounds"]], np.float32)
@@ -361,12 +364,55 @@ def extras(net, params, cfg, dev, world, args):
     from irbfn_b200.train import GraphedTrainStep
     gstep = GraphedTrainStep(state, x.shape[0], GB, loss="l2").load(x, y)
     ms_graph = timed(lambda: gstep(), args.steps, args.warmup)
+    # where the step's time goes: this rank's kernels alone (no collective: global batch = shard), the
+    # all-reduce of the flat gradient alone, and the rest (launch gaps, rank skew)
+    ms_local = timed(lambda: grad_step(state, x, y, x.shape[0]), args.steps, args.warmup)
+    ms_ar = timed(lambda: parallel.allreduce_sum_(state._grad_ext), args.steps, args.warmup) if world > 1 else 0.0
     fl = R * K * (3 * D + 2) + 2 * K * O + R * K * (5 * D + 9) + 4 * K * O
+    lane_step = R * K * (2 * D + 2) + K * O + R * K * (3 * D + 5) + 2 * K * O
     res["train_step_C3"] = {"global_batch": GB, "scaling": "strong", "ms_fwd_vjp_allreduce": ms_g,
                             "ms_with_clip_adam": ms_t, "ms_with_clip_adam_cuda_graph": ms_graph,
                             "samples_per_s": GB / (min(ms_t, ms_graph) * 1e-3),
                             "algorithmic_tflops": fl * GB / (ms_g * 1e-3) / 1e12,
-                            "allreduce_bytes": int(state.grad.numel() * 4)}
+                            "allreduce_bytes": int(state._grad_ext.numel() * 4)}
+    tail["c3"] = {"shape": "R12_K100_D8_O2", "global_batch": GB, "n_gpus": world, "ms_eager": ms_t, "ms_graph": ms_graph,
+                  "ms_kernels_this_rank": ms_local, "ms_allreduce_alone": ms_ar,
+                  "ms_fwd_vjp_allreduce": ms_g, "allreduce_bytes": int(state._grad_ext.numel() * 4),
+                  "lane_ops_T_per_s": lane_step * GB / (ms_g * 1e-3) / 1e12}
+
+    # 8(e) result check on hardware: the NCCL-reduced gradient of the sharded step against the gradient of
+    # the whole batch on one device (rank 0 holds the full batch too); per-leaf ||g - g1|| / ||g1||
+    grad_step(state, x, y, GB)
+    torch.cuda.synchronize()
+    if rank == 0:
+        full = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+        if world > 1:
+            grad_step(full, xall.to(dev), yall.to(dev), GB)
+            got, how = state, "NCCL all-reduce of %d shard gradients vs the full batch on rank 0" % world
+        else:
+            # one device: two half-batch shard gradients (means over the global batch) summed vs the full batch
+            h = GB // 2
+            halves = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+            acc = torch.zeros_like(halves.grad)
+            for lo_, hi_ in ((0, h), (h, GB)):
+                grad_step(halves, xall[lo_:hi_].to(dev), yall[lo_:hi_].to(dev), GB)   # world 1: the all-reduce is a no-op
+                acc += halves.grad
+            halves.grad.copy_(acc)
+            grad_step(full, xall.to(dev), yall.to(dev), GB)
+            got, how = halves, "two half-batch shard gradients summed vs the full batch (one device: no collective)"
+        worst = 0.0
+        for k in full.gviews:
+            ref = full.gviews[k].double()
+            worst = max(worst, float((got.gviews[k].double() - ref).norm() / ref.norm()))
+        tail["dp_parity"] = {"n_gpus": world, "rel_l2_max_over_leaves": worst, "tol": 1e-4, "ok": bool(worst <= 1e-4),
+                             "how": how}
+        del full
+
+    # the same step on the other shipped training shapes: the Cartesian C1 shape, and the
+    # five-step Frenet trainer's shape (train_step_fullint needs O = 10; shipped 27 x 500 x 8 -> 10)
+    for tag, fixture, loss in (("c3_c1shape", "c1_cartesian_1x1000.npz", "l2"),
+                               ("c3_o10_fullint", "warmstart_27x500_o10.npz", "frenet_fullint")):
+        tail[tag] = train_case(fixture, loss, GB, dev, rank, world, args, timed)
 
     # C4: input gradient for 1M queries per GPU (weak), dx of sum(y)
     B4 = 1000000
@@ -426,8 +472,41 @@ def extras(net, params, cfg, dev, world, args):
     del etab
     del tabx, taby, tab_
     if not args.no_other:
-        res.update(other_configs(dev, world, args, timed))
-    return res
+        other = other_configs(dev, world, args, timed)
+        tail["c5"] = other.pop("c5_summary")
+        res.update(other)
+    return res, tail
+
+
+def train_case(fixture, loss, GB, dev, rank, world, args, timed):
+    """One data-parallel optimiser step (forward, fused loss, VJP, all-reduce, clip + Adam) on a shipped shape."""
+    import torch
+    from irbfn_b200 import basis, parallel
+    from irbfn_b200.model import WCRBFNet, device_params
+    from irbfn_b200.train import GraphedTrainStep, TrainState, grad_step, train_step
+    cfg, pf = _fixture(fixture)
+    R, K, D, O = cfg["num_regions"], cfg["num_kernels"], cfg["in_features"], cfg["out_features"]
+    net = WCRBFNet(D, O, K, getattr(basis, cfg["basis_func"]), R, cfg["lower_bounds"], cfg["upper_bounds"],
+                   cfg["dimension_ranges"], cfg["activation_idx"], cfg["delta"])
+    params = device_params({"params": {"rbf_list": {"centers": pf["centers"], "log_sigs": pf["log_sigs"]},
+                                       "linear": {"kernel": pf["kernel"], "bias": pf["bias"]}}}, dev)
+    lo = np.array([min(b) for b in cfg["lower_bounds"]] + [-1.0] * D, np.float32)[:D]
+    hi = np.array([max(b) for b in cfg["upper_bounds"]] + [1.0] * D, np.float32)[:D]
+    a, b = parallel.shard_range(GB, rank, world)
+    g = torch.Generator().manual_seed(11)
+    x = (torch.rand((GB, D), generator=g) * torch.from_numpy(hi - lo) + torch.from_numpy(lo))[a:b].to(dev).contiguous()
+    y = torch.randn((GB, O), generator=g)[a:b].to(dev).contiguous()
+    state = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+    steps = max(3, args.steps // 2)
+    ms_g = timed(lambda: grad_step(state, x, y, GB, loss), steps, 3)
+    ms_t = timed(lambda: train_step(state, x, y, GB, loss), steps, 3)
+    gstep = GraphedTrainStep(state, x.shape[0], GB, loss=loss).load(x, y)
+    ms_graph = timed(lambda: gstep(), steps, 3)
+    lane = R * K * (2 * D + 2) + K * O + R * K * (3 * D + 5) + 2 * K * O
+    return {"shape": "R%d_K%d_D%d_O%d" % (R, K, D, O), "loss": loss, "global_batch": GB, "n_gpus": world,
+            "ms_eager": ms_t, "ms_graph": ms_graph, "ms_fwd_loss_vjp_allreduce": ms_g,
+            "lane_ops_T_per_s": lane * GB / (ms_g * 1e-3) / 1e12,
+            "allreduce_bytes": int(state._grad_ext.numel() * 4)}
 
 
 def _fixture(name):
@@ -472,6 +551,23 @@ def other_configs(dev, world, args, timed):
     res["forward_C1"] = {"queries": 4096, "shape": "R1_K1000_D7_O2_gaussian", "us_per_call": ms1 * 1e3,
                          "us_per_call_in_cuda_graph": ms1g * 1e3, "queries_per_s": 4096 / (ms1 * 1e-3),
                          "queries_per_s_in_cuda_graph": 4096 / (ms1g * 1e-3)}
+    if world == 1 and not args.no_cpu:
+        # BASELINE config 1 names the CPU comparison: the same 4,096-query call through the C/OpenMP oracle port
+        from oracle import c_oracle
+        cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        x1h = x1.cpu().numpy()
+        run1 = lambda: c_oracle.forward(x1h, p["centers"], p["log_sigs"], p["kernel"], p["bias"], 0, cfg=cfg, nthreads=cores)
+        y1c = run1()
+        t0 = time.perf_counter()
+        reps = 0
+        while reps < 20 or time.perf_counter() - t0 < 2.0:
+            run1()
+            reps += 1
+        dt1 = (time.perf_counter() - t0) / reps
+        res["forward_C1"]["cpu_baseline"] = {"value": 4096 / dt1, "unit": UNIT, "us_per_call": dt1 * 1e6, "cores": cores,
+                                             "kind": "port", "sample": "the same 4,096 queries, %d calls of "
+                                             "oracle/irbfn_oracle.c (float32, OpenMP)" % reps}
+        res["forward_C1"]["parity_vs_cpu"] = float(np.abs(y1.cpu().numpy() - y1c).max() / np.abs(y1c).max())
 
     # C2b: readout share 43 %
     cfg, p = _fixture("c2b_frenet_1x1000_o10.npz")
@@ -515,6 +611,10 @@ def other_configs(dev, world, args, timed):
     res["fwd_vjp_C5"] = {"queries_per_gpu": B5b, "ms": ms5b, "queries_per_s": world * B5b / (ms5b * 1e-3),
                          "algorithmic_tflops": (R * K * (3 * D + 2) + R * K * (5 * D + 9) + 6 * K * O) * B5b
                                                / (ms5b * 1e-3) / 1e12, "timed_steps": 2, "warmup": 1}
+    lane5b = lane5 + R * K * (3 * D + 5) + 2 * K * O
+    res["c5_summary"] = {"shape": "R64_K4096_D6_O16", "n_gpus": world, "fwd_ms_per_2p24": ms5,
+                         "fwd_lane_ops_T_per_s": lane5 * B5 / (ms5 * 1e-3) / 1e12,
+                         "fwd_vjp_ms_per_2p22": ms5b, "fwd_vjp_lane_ops_T_per_s": lane5b * B5b / (ms5b * 1e-3) / 1e12}
     return res
 
 

@@ -125,6 +125,17 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
                   void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
 
 /*
+ * Training-step forward: irbfn_forward with the tanh gate, which also writes the gate gamma (B,R) it
+ * computes on the fly (model.py:70-95).  Handing that buffer to irbfn_backward as its external `gate`
+ * (gd = NULL) saves the backward's own gate pass -- what jax.value_and_grad's forward residuals would
+ * hold for scripts/train_nmpc.py:297.  gate_out must not be NULL.
+ */
+int irbfn_forward_gate(const float* x, const float* centers, const float* log_sigs, const float* W,
+                       const float* bias, const IrbfnGateDesc* gd, float* y, float* gate_out,
+                       int64_t B, int R, int K, int D, int O, int basis,
+                       void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
+
+/*
  * Backward (VJP).  Recomputes phi from x and the parameters; nothing from the forward is saved.
  *
  *   dy        (B,O)    cotangent of y, or NULL (then W may be NULL too)
@@ -234,6 +245,31 @@ size_t irbfn_clip_adam_workspace_bytes(int64_t n);
 int irbfn_clip_adam(float* params, float* grad, float* mu, float* nu, int64_t n, double* step_count, double lr,
                     double b1, double b2, double eps, double max_norm, float* grad_norm, void* workspace,
                     size_t workspace_bytes, irbfn_stream_t stream);
+
+/*
+ * The tail of a data-parallel training step in ONE launch: [one-shot all-reduce of the flat gradient over
+ * NVLink peer memory] -> global norm -> clip_by_global_norm -> Adam (scripts/train_nmpc.py:231-236,299), for
+ * gradients of at most irbfn_fused_update_max_n() floats (the shipped NMPC shapes hold 10-20 k): at that size
+ * ncclAllReduce + the two optimiser launches are pure latency.
+ *
+ *   peers    device array of `world` pointers: rank r's symmetric buffer mapped into this process
+ *            (peers[rank] is this rank's own), each irbfn_fused_update_buffer_bytes(n + n_extra, world) bytes,
+ *            zero-filled once before the first call.  This rank's backward writes its LOCAL gradient into
+ *            peers[rank][0 .. n) and up to n_extra more floats (the loss) behind it; the words after the data
+ *            are flags owned by the kernel.  NULL with world == 1: `reduced` then already holds the gradient.
+ *   reduced  [n + n_extra] local: receives the sum over ranks (same summation order on every rank, so the
+ *            replicated parameters stay bit-identical); its first n floats are clipped in place by the update
+ *   apply_update  0: all-reduce only
+ *   status   optional device int, set to 1 if a peer did not arrive within ~20 s
+ * Every rank must make the same sequence of calls.  Graph-capturable (the step sequence number lives in the
+ * buffer).  IRBFN_ERR_BAD_DIMS when n + n_extra exceeds the limit: use NCCL + irbfn_clip_adam.
+ */
+int64_t irbfn_fused_update_max_n(void);
+size_t irbfn_fused_update_buffer_bytes(int64_t n_total, int world);
+int irbfn_fused_update(float* params, float* mu, float* nu, float* reduced, int64_t n, int n_extra,
+                       float* const* peers, int rank, int world, int apply_update, double* step_count,
+                       double lr, double b1, double b2, double eps, double max_norm, float* grad_norm,
+                       int* status, irbfn_stream_t stream);
 
 /*
  * Plain rollouts (what irbfn_planner.py:212-214,510-518 and the losses call):

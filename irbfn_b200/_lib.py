@@ -31,12 +31,14 @@ DYN_FRENET_MULT, DYN_FRENET_ONESTEP_AUX, DYN_ST_MULT, DYN_ST_ONESTEP_AUX = 0, 1,
 # every symbol include/irbfn_b200.h declares (tests check the .so exports exactly these)
 EXPORTED_SYMBOLS = (
     "irbfn_abi_version", "irbfn_error_string", "irbfn_last_error_detail", "irbfn_forward_workspace_bytes", "irbfn_forward",
+    "irbfn_forward_gate",
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_forward_plan",
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
     "irbfn_gather_rows", "irbfn_grid_index", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
     "irbfn_prediction_loss_workspace_bytes", "irbfn_prediction_loss",
     "irbfn_clip_adam_workspace_bytes", "irbfn_clip_adam",
+    "irbfn_fused_update_max_n", "irbfn_fused_update_buffer_bytes", "irbfn_fused_update",
 )
 
 
@@ -80,6 +82,8 @@ def load():
     lib.irbfn_forward.restype = i
     lib.irbfn_forward.argtypes = [p, p, p, p, p, p, C.POINTER(GateDesc), p, p, i64, i, i, i, i, i,
                                   p, sz, p]
+    lib.irbfn_forward_gate.restype = i
+    lib.irbfn_forward_gate.argtypes = [p, p, p, p, p, C.POINTER(GateDesc), p, p, i64, i, i, i, i, i, p, sz, p]
     lib.irbfn_backward_workspace_bytes.restype = sz
     lib.irbfn_backward_workspace_bytes.argtypes = [i64, i, i, i, i, u]
     lib.irbfn_backward.restype = i
@@ -102,6 +106,13 @@ def load():
     lib.irbfn_clip_adam.restype = i
     lib.irbfn_clip_adam.argtypes = [p, p, p, p, i64, p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
                                     p, p, sz, p]
+    lib.irbfn_fused_update_max_n.restype = i64
+    lib.irbfn_fused_update_max_n.argtypes = []
+    lib.irbfn_fused_update_buffer_bytes.restype = sz
+    lib.irbfn_fused_update_buffer_bytes.argtypes = [i64, i]
+    lib.irbfn_fused_update.restype = i
+    lib.irbfn_fused_update.argtypes = [p, p, p, p, i64, i, p, i, i, i, p, C.c_double, C.c_double, C.c_double,
+                                       C.c_double, C.c_double, p, p, p]
     lib.irbfn_dynamics_loss.restype = i
     lib.irbfn_dynamics_loss.argtypes = [i, p, p, p, C.POINTER(C.c_float), p, p, i64, i, i, i64, p, sz, p]
     lib.irbfn_integrate.restype = i

@@ -182,14 +182,35 @@ size_t irbfn_forward_workspace_bytes(int64_t B, int R, int K, int D, int O, int 
     device_info(&sms, &smem);   // keeps the nominal B200 value when no device is present
     int kps;
     int ns = fwd_split(B, R, K, sms, &kps);
-    if (const char* dv = getenv("IRBFN_DEV_KPS")) { kps = atoi(dv); ns = (K + kps - 1) / kps; }
     return ns > 1 ? (size_t)ns * (size_t)B * (size_t)O * sizeof(float) : 0;
 }
+
+static int forward_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
+                        const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
+                        float* hidden, float* gate_out, int64_t B, int R, int K, int D, int O, int basis,
+                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
 
 int irbfn_forward(const float* x, const float* centers, const float* log_sigs, const float* W,
                   const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
                   float* hidden, int64_t B, int R, int K, int D, int O, int basis, void* workspace,
                   size_t workspace_bytes, irbfn_stream_t stream) {
+    return forward_impl(x, centers, log_sigs, W, bias, gate, gd, y, hidden, nullptr, B, R, K, D, O, basis,
+                        workspace, workspace_bytes, stream);
+}
+
+int irbfn_forward_gate(const float* x, const float* centers, const float* log_sigs, const float* W,
+                       const float* bias, const IrbfnGateDesc* gd, float* y, float* gate_out, int64_t B,
+                       int R, int K, int D, int O, int basis, void* workspace, size_t workspace_bytes,
+                       irbfn_stream_t stream) {
+    if (gd == nullptr || gate_out == nullptr) return IRBFN_ERR_NULL_POINTER;
+    return forward_impl(x, centers, log_sigs, W, bias, nullptr, gd, y, nullptr, gate_out, B, R, K, D, O, basis,
+                        workspace, workspace_bytes, stream);
+}
+
+static int forward_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
+                        const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
+                        float* hidden, float* gate_out, int64_t B, int R, int K, int D, int O, int basis,
+                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream) {
     if (B < 0 || R <= 0 || K <= 0 || D <= 0) return IRBFN_ERR_BAD_DIMS;
     if (y != nullptr && O <= 0) return IRBFN_ERR_BAD_DIMS;
     if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
@@ -218,7 +239,6 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
     // Without (enough) workspace the unsplit path runs -- same result, more latency.
     int k_per_split = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
     int nsplit = fwd_split(B, R, K, dev.sms, &k_per_split);
-    if (const char* dv = getenv("IRBFN_DEV_KPS")) { k_per_split = atoi(dv); nsplit = (K + k_per_split - 1) / k_per_split; }
     float* part = nullptr;
     if (nsplit > 1 && y != nullptr) {
         if (workspace != nullptr && workspace_bytes >= (size_t)nsplit * (size_t)B * (size_t)O * sizeof(float))
@@ -247,6 +267,7 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
         a.gd = gdev;
         a.y = ocur > 0 ? (part ? part : y) : nullptr;
         a.hidden = first ? hidden : nullptr;
+        a.gate_out = first ? gate_out : nullptr;
         a.B = B;
         a.R = R;
         a.K = K;

@@ -262,9 +262,10 @@ static bool bwd_layout(int64_t B, int R, int K, int D, int O, unsigned mask, int
             if (o0 == 0) L->pplan = pp;
             if (pp.part_floats > max_part) max_part = pp.part_floats;
             BwdPWPlan pw;   // the region-lane kernel may take this window instead: size for either
-            if (bwdpw_applies(R, O, has_dhid) && plan_bwd_pw(B, R, K, DT, O, fwd_ot_for(ocur), sms, smem, &pw) &&
-                pw.part_floats > max_part)
-                max_part = pw.part_floats;
+            if (bwdpw_applies(R, O, has_dhid) && plan_bwd_pw(B, R, K, DT, O, fwd_ot_for(ocur), sms, smem, &pw)) {
+                if (pw.part_floats > max_part) max_part = pw.part_floats;
+                if (pw.splits > max_splits) max_splits = pw.splits;
+            }
             if (pp.splits > max_splits) max_splits = pp.splits;
             o0 += ocur;
         } while (o0 < O);
@@ -272,8 +273,8 @@ static bool bwd_layout(int64_t B, int R, int K, int D, int O, unsigned mask, int
         L->part_off = off;
         off = align256(off + max_part * sizeof(float));
         L->partdb_off = off;
-        off = align256(off + (size_t)kDbBlocks * (O > 0 ? O : 1) * sizeof(float));
-        (void)max_splits;
+        const int db_rows = max_splits > kDbBlocks ? max_splits : kDbBlocks;
+        off = align256(off + (size_t)db_rows * (O > 0 ? O : 1) * sizeof(float));
     }
     if (L->need_x) {
         if (tanh_gate && (mask & IRBFN_GRAD_X)) { L->dgate_off = off; off = align256(off + (size_t)B * R * sizeof(float)); }
@@ -360,6 +361,9 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             const int OT = fwd_ot_for(ocur);
             BwdPPlan pp;
             BwdPWPlan pw;
+            // the bias gradient's column sums of dy ride along in the chunk-0 CTAs (one thread per column and
+            // row phase); outputs wider than a CTA has threads fall back to the separate pass
+            const bool in_kernel_db = (grad_mask & IRBFN_GRAD_KERNEL) && Oeff > 0 && Oeff <= 128;
             const bool wide = bwdpw_applies(R, Oeff, dhidden != nullptr) && plan_bwd_pw(B, R, K, DT, Oeff, OT, sms, smem, &pw);
             if (wide) {
                 // several regions share a wide readout: lanes = regions, dh from a per-tile table, dW from the
@@ -369,6 +373,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
                 BwdPWArgs w{};
                 w.x = x; w.centers = centers; w.log_sigs = log_sigs; w.W = W; w.gate = gate_p; w.dy = dy;
                 w.part = (float*)(ws + L.part_off);
+                w.part_db = (first && in_kernel_db) ? (float*)(ws + L.partdb_off) : nullptr;
                 w.B = B; w.R = R; w.K = K; w.Dsrc = D; w.O = Oeff;
                 w.G = pw.G; w.NRG = pw.NRG; w.units = pw.units; w.units_per_cta = pw.units_per_cta;
                 w.nchunks = pw.nchunks; w.splits = pw.splits; w.TQ = pw.TQ; w.Kspan = pw.Kspan;
@@ -392,6 +397,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             a.x = x; a.centers = centers; a.log_sigs = log_sigs; a.W = W; a.gate = gate_p;
             a.dy = dy; a.dhidden = dhidden;
             a.part = (float*)(ws + L.part_off);
+            a.part_db = (first && in_kernel_db) ? (float*)(ws + L.partdb_off) : nullptr;
             a.B = B; a.R = R; a.K = K; a.Dsrc = D; a.O = Oeff; a.o0 = o0; a.ocur = ocur;
             a.nchunks = pp.nchunks; a.splits = pp.splits; a.pairs_per_chunk = pp.pairs_per_chunk; a.ppw = pp.ppw;
             a.TQ = pp.TQ; a.Kspan = pp.Kspan; a.Rspan = pp.Rspan;
@@ -413,11 +419,11 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             r.dLS = (first && (grad_mask & IRBFN_GRAD_LOG_SIGS)) ? dlog_sigs : nullptr;
             r.dW = ((grad_mask & IRBFN_GRAD_KERNEL) && ocur > 0) ? dW : nullptr;
             r.db = (first && (grad_mask & IRBFN_GRAD_KERNEL) && Oeff > 0) ? dbias : nullptr;
-            r.splits = pp.splits; r.db_blocks = kDbBlocks; r.R = R; r.K = K; r.D = DT; r.Dsrc = D; r.PW = pp.PW;
+            r.splits = pp.splits; r.db_blocks = in_kernel_db ? pp.splits : kDbBlocks; r.R = R; r.K = K; r.D = DT; r.Dsrc = D; r.PW = pp.PW;
             r.O = Oeff; r.o0 = o0; r.ocur = ocur;
             const long long n = ((r.dC || r.dLS) ? (long long)R * K * (DT + 1) : 0) +
                                 (r.dW ? (long long)K * ocur : 0) + (r.db ? Oeff : 0);
-            if (r.db != nullptr) {
+            if (r.db != nullptr && !in_kernel_db) {
                 db_partial_kernel<<<kDbBlocks, 256, 0, st>>>(dy, (float*)(ws + L.partdb_off), B, Oeff);
                 { const cudaError_t ce = cudaGetLastError(); if (ce != cudaSuccess) return note_cuda_error("db_partial_kernel", (int)ce); }
             }

@@ -38,6 +38,7 @@ struct BwdPArgs {
     const float* dy;        // (B,O) or nullptr
     const float* dhidden;   // (B,K) or nullptr
     float* part;            // [splits][R*K][PW]   PW = D + 1 + OT
+    float* part_db;         // [splits][O] column sums of dy (the bias gradient's partials), or nullptr
     long long B;
     int R, K, Dsrc, O;
     int o0, ocur;           // dW column window of this launch
@@ -56,6 +57,37 @@ __device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Bias gradient db[o] = sum_q dy[q][o], taken by the CTAs of chunk 0 (one per split) while a tile's dy rows
+// sit in shared memory: thread (phase, column) adds every nph-th row of its column into a shared-memory
+// accumulator; the phases are combined in phase order at the end.  Replaces a separate pass over dy
+// (db_partial_kernel).  Everything is recomputed from the kernel arguments at each use and the running sums
+// live in shared memory, so the hot loop keeps its registers (the 640-thread variant sits at its 96-register
+// cap: holding this state in registers spilled and cost 12 % of the kernel).
+constexpr int kDbScratch = 1024;   // floats reserved at the end of dynamic shared memory (>= threads per CTA)
+__device__ __forceinline__ bool db_active(const float* part_db, const float* dy, int chunk, int O, int NT) {
+    return part_db != nullptr && dy != nullptr && chunk == 0 && O > 0 && O <= NT;
+}
+__device__ __forceinline__ void db_tile(float* dbs, const float* dys, int DS, int tq, int O, int NT, int tid) {
+    int nph = NT / O;
+    if (nph > 32) nph = 32;
+    if (tid < nph * O) {
+        const int o = tid % O, ph = tid / O;
+        float s = 0.f;
+        for (int q = ph; q < tq; q += nph) s += dys[(size_t)q * DS + o];
+        dbs[tid] += s;
+    }
+}
+__device__ __forceinline__ void db_flush(const float* dbs, float* part_db, int split, int O, int NT, int tid) {
+    __syncthreads();
+    int nph = NT / O;
+    if (nph > 32) nph = 32;
+    if (tid < O) {
+        float s = 0.f;
+        for (int p = 0; p < nph; ++p) s += dbs[p * O + tid];
+        part_db[(size_t)split * O + tid] = s;
+    }
+}
 
 // shared-memory row strides (floats); must match bwdp_smem_floats in irbfn_plan.h
 __host__ __device__ constexpr int bwdp_xs(int D) { return ((D + 3) / 4) * 4; }
@@ -141,6 +173,8 @@ __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bw
     }
 
     const long long ntiles = (a.B + TQ - 1) / TQ;
+    float* dbs = dhs + (DHT ? 0 : (size_t)TQ * Kspan);   // bias-gradient accumulators: kDbScratch floats at the end
+    if (tid < kDbScratch) dbs[tid] = 0.f;
 
     auto issue_tile = [&](long long tile, int stage) {
         float* sb = smem + (size_t)stage * stage_floats;
@@ -247,6 +281,7 @@ __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bw
         cp_async_wait_all();
         __syncthreads();  // stage landed; everyone is done computing on the other stage
         if (tile + a.splits < ntiles) issue_tile(tile + a.splits, stage ^ 1);
+        if (db_active(a.part_db, a.dy, chunk, O, NT)) db_tile(dbs, sb + st_dy, DS, tq, O, NT, tid);
 
         if (!DHT) {
             // ---- dh table of the tile: dh[q][k] = dy[q,:] . W[k,:] (+ dhidden[q][k]) ----
@@ -273,6 +308,7 @@ __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bw
         if (!DHT) __syncthreads();  // the dh table is rebuilt by the next tile
     }
     cp_async_wait_all();
+    if (db_active(a.part_db, a.dy, chunk, O, NT)) db_flush(dbs, a.part_db, split, O, NT, tid);
 
     // ---- flush raw partial sums (the reduce kernel applies 2 exp(-2 log_sig)) ----
     float* part = a.part + (size_t)split * RK * PW;

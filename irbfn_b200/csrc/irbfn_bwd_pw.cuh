@@ -42,6 +42,7 @@ struct BwdPWArgs {
     const float* gate;      // (B,R)
     const float* dy;        // (B,O)
     float* part;            // [splits][R*K][PW]   PW = D + 1 + OT
+    float* part_db;         // [splits][O] column sums of dy (bias gradient partials), or nullptr
     long long B;
     int R, K, Dsrc, O;
     int G;                  // lanes per region group (power of two, <= 32)
@@ -128,6 +129,8 @@ __global__ void __launch_bounds__((OT <= 10 && D <= 7) ? 512 : 384, 1) irbfn_bwd
     const long long gpitch = (long long)a.R * (long long)sizeof(float);   // bytes between gate rows
     const int dhpitch2 = 2 * Kspan;                                       // floats between dh rows two queries apart
     const long long ntiles = (a.B + TQ - 1) / TQ;
+    float* dbs = Ws + (size_t)Kspan * WS + (size_t)(NT / 32) * 32 * LS;   // after the warps' scratch: kDbScratch floats
+    if (tid < kDbScratch) dbs[tid] = 0.f;
     auto issue_tile = [&](long long tile, int stage) {
         float* sb = smem + (size_t)stage * stage_floats;
         const long long q0 = tile * TQ;
@@ -155,6 +158,7 @@ __global__ void __launch_bounds__((OT <= 10 && D <= 7) ? 512 : 384, 1) irbfn_bwd
         cp_async_wait_all();
         __syncthreads();   // stage landed; everyone is done with the other stage and with the dh table
         if (tile + a.splits < ntiles) issue_tile(tile + a.splits, stage ^ 1);
+        if (db_active(a.part_db, a.dy, chunk, O, NT)) db_tile(dbs, sb + st_dy, DS, tq, O, NT, tid);
 
         // ---- dh table of the tile: dh[q][c] = dy[q,:] . W[kp_lo*2 + c, :] ----
         // one thread per query: its dy row in registers, the readout rows as broadcast LDS.128
@@ -322,6 +326,7 @@ __global__ void __launch_bounds__((OT <= 10 && D <= 7) ? 512 : 384, 1) irbfn_bwd
         }
     }
     cp_async_wait_all();
+    if (db_active(a.part_db, a.dy, chunk, O, NT)) db_flush(dbs, a.part_db, split, O, NT, tid);
 
     // ---- dW: total over the group's lanes (fixed butterfly order), kept by the group's first lane ----
     for (int m = G >> 1; m >= 1; m >>= 1) {

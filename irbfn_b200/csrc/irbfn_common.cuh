@@ -194,6 +194,8 @@ struct FwdArgs {
     GateDev gd;
     float* y;               // (B,ldw) or nullptr
     float* hidden;          // (B,K) or nullptr
+    float* gate_out;        // (B,R) or nullptr: the fused tanh gate is also written out (training: the
+                            // parameter-gradient kernel reads it instead of recomputing it)
     long long B;
     int R, K;
     int Dsrc;               // features in memory (<= the kernel's compiled D; the rest is zero-padded)

@@ -96,6 +96,21 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
             } else {
                 gate_columns(a.gd, a.x, q0, a.B, a.Dsrc, r0, rc, gcol, NT);
             }
+            if (a.gate_out != nullptr && blockIdx.y == 0) {
+                // training: the gate goes out to (B,R) for the parameter-gradient kernel.  A warp owns 128
+                // consecutive queries, i.e. 128 * rc consecutive floats of the (B,R) rows when rc == R: its lanes
+                // copy them out of the warp's own table columns, coalesced (thread-private scattered 4-byte
+                // stores cost 40 % of the kernel; a CTA-wide copy needs two barriers per tile).
+                __syncwarp();
+                const int w0 = (tid >> 5) * 32;                         // first thread of this warp
+                const long long qw0 = (long long)tile * TQ + (long long)w0 * Q;
+                const int nq = (int)max(0ll, min((long long)(32 * Q), a.B - qw0));
+                for (int e = tid & 31; e < nq * rc; e += 32) {
+                    const int q = e / rc, rr = e - q * rc;
+                    a.gate_out[(qw0 + q) * R + r0 + rr] = gtab[((size_t)rr * NT + w0 + (q >> 2)) * 4 + (q & 3)];
+                }
+                __syncwarp();
+            }
 
             for (int kch = 0; kch < n_kch; ++kch) {
                 const int k0 = kb + kch * KC;

@@ -160,12 +160,14 @@ struct BwdPPlan {
 inline int bwdp_xs_h(int D) { return ((D + 3) / 4) * 4; }
 inline int bwdp_ds_h(int O) { return O <= 0 ? 0 : (O <= 2 ? 2 : ((O + 3) / 4) * 4); }
 
+constexpr int kDbScratch_h = 1024;   // bias-gradient accumulators at the end of shared memory (kDbScratch in irbfn_bwd_p.cuh)
+
 inline size_t bwdp_smem_floats(int TQ, int D, int O, int Kspan, int Rspan, int has_dhid, int dht) {
     size_t st = (size_t)TQ * bwdp_xs_h(D) + (size_t)TQ * bwdp_ds_h(O) + (size_t)TQ * (Rspan + 1);
     st = ((st + 3) / 4) * 4;
     st += has_dhid ? (size_t)TQ * Kspan : 0;
     st = ((st + 3) / 4) * 4;
-    return 2 * st + (dht ? 0 : (size_t)TQ * Kspan);
+    return 2 * st + (dht ? 0 : (size_t)TQ * Kspan) + kDbScratch_h;
 }
 
 inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT, int has_dhid, int sms,
@@ -255,7 +257,7 @@ inline size_t bwdpw_smem_floats(int TQ, int D, int O, int OT, int Kspan, int NW)
     const int WS = ((OT + 3) / 4) * 4, DS = WS + (WS % 8 == 0 ? 4 : 0);   // must match irbfn_bwd_pw.cuh
     size_t st = (size_t)TQ * bwdp_xs_h(D) + (size_t)TQ * DS;
     st = ((st + 3) / 4) * 4;
-    return 2 * st + (size_t)TQ * Kspan + (size_t)Kspan * WS + (size_t)NW * 32 * kPwLS_h;
+    return 2 * st + (size_t)TQ * Kspan + (size_t)Kspan * WS + (size_t)NW * 32 * kPwLS_h + kDbScratch_h;
 }
 
 inline bool plan_bwd_pw(long long B, int R, int K, int D, int O, int OT, int sms, int smem_limit, BwdPWPlan* p) {

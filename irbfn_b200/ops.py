@@ -18,7 +18,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
 
 __all__ = [
     "GatePack", "forward", "backward", "region_gate", "softmax_gate", 
-    "dynamics_loss", "integrate", "default_dyn_params", "jacobian",
+    "dynamics_loss", "integrate", "default_dyn_params", "jacobian", "fused_update_", "fused_update_max_n",
     "gather_rows", "GridKeys", "grid_index", "nearest_row",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
     "GRAD_X", "GRAD_GATE", "GRAD_PARAMS",
@@ -90,10 +90,12 @@ class GatePack:
 
 def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: GatePack = None,
             basis: int = BASIS_GAUSSIAN, want_y: bool = True, want_hidden: bool = False,
-            out=None, split: bool = True):
+            out=None, split: bool = True, gate_out=None):
     """y (B,O) and/or hidden (B,K) of the fused IRBFN forward (irbfn_forward).  ``split=False`` withholds
     the workspace, so a small batch runs as ONE CTA per query tile instead of spreading its kernels over
-    the device -- what a caller wants when it keeps the device busy with several launches at once."""
+    the device -- what a caller wants when it keeps the device busy with several launches at once.
+    ``gate_out`` (B,R): the tanh gate is written there too (irbfn_forward_gate; training steps hand it to
+    ``backward`` as its external gate)."""
     lib = _lib.load()
     _chk(x, "x")
     B, D = x.shape
@@ -126,9 +128,16 @@ def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: Gate
     with torch.cuda.device(x.device):
         nbytes = lib.irbfn_forward_workspace_bytes(B, R, K, D, O, 1 if gd is not None else 0) if split else 0
         ws = _workspace(nbytes, x.device)       # partial readouts of the small-batch split-K path
-        rc = lib.irbfn_forward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias),
-                               _ptr(gate), gd.ref() if gd is not None else None, _ptr(y),
-                               _ptr(hidden), B, R, K, D, O, basis, _ptr(ws), nbytes, _stream())
+        if gate_out is not None:
+            if gd is None or not want_y or want_hidden:
+                raise ValueError("gate_out needs the tanh gate (gd) and the plain y output")
+            _chk(gate_out, "gate_out", (B, R))
+            rc = lib.irbfn_forward_gate(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias), gd.ref(),
+                                        _ptr(y), _ptr(gate_out), B, R, K, D, O, basis, _ptr(ws), nbytes, _stream())
+        else:
+            rc = lib.irbfn_forward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias),
+                                   _ptr(gate), gd.ref() if gd is not None else None, _ptr(y),
+                                   _ptr(hidden), B, R, K, D, O, basis, _ptr(ws), nbytes, _stream())
     _lib.check(rc, "irbfn_forward")
     if want_y and want_hidden:
         return y, hidden
@@ -321,6 +330,35 @@ def clip_adam_(params, grad, mu, nu, step_count, lr: float, b1: float = 0.9, b2:
         rc = lib.irbfn_clip_adam(_ptr(params), _ptr(grad), _ptr(mu), _ptr(nu), n, _ptr(step_count), lr, b1, b2, eps,
                                  max_norm, _ptr(grad_norm), _ptr(ws), nbytes, _stream())
     _lib.check(rc, "irbfn_clip_adam")
+    return grad_norm
+
+
+def fused_update_max_n() -> int:
+    return int(_lib.load().irbfn_fused_update_max_n())
+
+
+def fused_update_(params, mu, nu, reduced, n: int, n_extra: int, step_count, lr: float, b1: float = 0.9,
+                  b2: float = 0.999, eps: float = 1e-8, max_norm: float = 0.0, grad_norm=None, peers=None,
+                  rank: int = 0, world: int = 1, apply_update: bool = True, status=None):
+    """Tail of a data-parallel training step in ONE launch (irbfn_fused_update): optional one-shot all-reduce
+    over NVLink peer memory (``peers``: int64 device tensor of the ranks' symmetric-buffer addresses, see
+    parallel.PeerBuffer), then clip_by_global_norm + Adam on the flat buffers.  ``reduced`` (n + n_extra floats)
+    receives the summed gradient; with ``peers=None`` it already holds it."""
+    lib = _lib.load()
+    _chk(reduced, "reduced")
+    if reduced.numel() < n + n_extra:
+        raise ValueError("reduced holds %d floats, need %d" % (reduced.numel(), n + n_extra))
+    if apply_update:
+        for t, name in ((params, "params"), (mu, "mu"), (nu, "nu")):
+            _chk(t, name, (n,))
+        _chk(step_count, "step_count", dtype=torch.float64)
+    if peers is not None and (peers.dtype != torch.int64 or peers.numel() != world or not peers.is_cuda):
+        raise ValueError("peers must be an int64 CUDA tensor with one address per rank")
+    with torch.cuda.device(reduced.device):
+        rc = lib.irbfn_fused_update(_ptr(params), _ptr(mu), _ptr(nu), _ptr(reduced), n, n_extra, _ptr(peers), rank, world,
+                                    1 if apply_update else 0, _ptr(step_count), lr, b1, b2, eps, max_norm,
+                                    _ptr(grad_norm), _ptr(status), _stream())
+    _lib.check(rc, "irbfn_fused_update")
     return grad_norm
 
 

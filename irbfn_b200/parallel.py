@@ -66,3 +66,87 @@ def allreduce_max_scalar(value: float, device=None) -> float:
 def barrier():
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
         dist.barrier()
+
+
+class PeerBuffer:
+    """A flat fp32 buffer of this rank that every other rank of the node can read (and flag) directly over
+    NVLink / NVSwitch: the memory side of ``ops.fused_update_`` (one-shot all-reduce fused with the optimiser
+    update).  One process per GPU: the buffers are exchanged as CUDA IPC handles through
+    the process group (torch's own ``_share_cuda_`` / ``_new_shared_cuda`` storage plumbing -- the mechanism
+    torch.multiprocessing uses), falling back to torch symmetric memory.
+
+    ``local``   this rank's buffer (n_total floats, then the kernel's flag words), zero-filled
+    ``ptrs``    int64 device tensor: address of rank r's buffer in THIS process
+    Construction is collective (every rank must call it) and raises if peer memory cannot be set up; callers
+    fall back to NCCL."""
+
+    def __init__(self, n_total: int, device, group=None):
+        from . import _lib
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("PeerBuffer needs an initialised process group")
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        device = torch.device(device)
+        nfloats = int(_lib.load().irbfn_fused_update_buffer_bytes(int(n_total), self.world)) // 4
+        self._keep = []
+        self.how = None
+        err = None
+        first, second = (self._init_symm, "symmetric-memory"), (self._init_ipc, "cuda-ipc")
+        if os.environ.get("IRBFN_PEER_MEMORY", "") == "ipc":
+            first, second = second, first
+        try:
+            first[0](nfloats, device, group)
+            self.how = first[1]
+        except Exception as e:           # noqa: BLE001 - any failure means: try the other mechanism
+            err = e
+        ok = torch.tensor([1 if self.how else 0], device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok.item()) == 0:
+            self.how = None
+            try:
+                second[0](nfloats, device, group)
+                self.how = second[1]
+            except Exception as e:       # noqa: BLE001
+                err = e
+            ok = torch.tensor([1 if self.how else 0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
+                raise RuntimeError("peer memory unavailable on this node: %r" % (err,))
+        self.n_total = int(n_total)
+        self.local.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(group)              # nobody flags a buffer that is not zeroed yet
+
+    def _init_ipc(self, nfloats, device, group):
+        # a dedicated cudaMalloc block (not a slice of the caching allocator's pool shared with other tensors)
+        self.local = torch.empty(max(nfloats, 1 << 19), device=device, dtype=torch.float32)[:nfloats]
+        handle = self.local.untyped_storage()._share_cuda_()
+        offset_bytes = self.local.storage_offset() * 4
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, (handle, offset_bytes), group=group)
+        addrs = []
+        for r, (h, off) in enumerate(gathered):
+            if r == self.rank:
+                addrs.append(self.local.data_ptr())
+                continue
+            (dev_idx, ipc_handle, size_bytes, blk_off, ref_h, ref_off, ev_h, ev_sync) = h
+            st = torch.UntypedStorage._new_shared_cuda(device.index, ipc_handle, size_bytes, blk_off, ref_h, ref_off,
+                                                       ev_h, ev_sync)
+            self._keep.append(st)
+            addrs.append(st.data_ptr() + off)
+            # kernels of THIS device dereference the peer's memory: peer access must be on in that direction
+            import ctypes
+            rt = ctypes.CDLL("libcudart.so.12")
+            rc = rt.cudaDeviceEnablePeerAccess(int(dev_idx), 0)
+            rt.cudaGetLastError()        # "already enabled" must not linger as the thread's last error
+            if rc not in (0, 704):       # 704 = cudaErrorPeerAccessAlreadyEnabled
+                raise RuntimeError("cudaDeviceEnablePeerAccess(%d) -> %d" % (dev_idx, rc))
+        torch.cuda.synchronize(device)
+        self.ptrs = torch.tensor(addrs, dtype=torch.int64, device=device)
+
+    def _init_symm(self, nfloats, device, group):
+        import torch.distributed._symmetric_memory as symm
+        t = symm.empty(nfloats, dtype=torch.float32, device=device)
+        h = symm.rendezvous(t, group if group is not None else dist.group.WORLD)
+        self.local = t
+        self._keep.append(h)
+        self.ptrs = torch.tensor([int(v) for v in h.buffer_ptrs], dtype=torch.int64, device=device)

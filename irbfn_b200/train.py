@@ -73,6 +73,35 @@ class TrainState:
         self.grad_norm = torch.zeros(1, device=device, dtype=torch.float32)
         self.dyn_params = ops.default_dyn_params()   # scripts/train_nmpc_frenet.py:322-338
         self.loss_terms = None
+        # Where the backward writes this rank's LOCAL gradient (+ the loss behind it).  One process: the reduced
+        # buffer itself.  Several ranks with NVLink peer memory: this rank's symmetric buffer, which the fused
+        # all-reduce + update kernel of every rank reads (enable_peer_allreduce); otherwise NCCL reduces in place.
+        self._grad_src = self._grad_ext
+        self.peer = None
+        self.peer_status = None
+        self.gate_buf = None          # (B,R) gate written by the forward, read by the backward
+        self.fused_tail = n + 1 <= ops.fused_update_max_n() if device.type == "cuda" else False
+
+    def enable_peer_allreduce(self) -> str:
+        """Collective.  Switch the gradient all-reduce of this state from NCCL to the one-shot kernel over
+        NVLink peer memory fused with clip + Adam (``ops.fused_update_``), when the gradient is small enough
+        and peer memory can be mapped.  Returns how the gradient is reduced afterwards: 'peer:<mechanism>' or
+        'nccl:<reason>'."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+            return "single-process"
+        if self.peer is not None:
+            return "peer:" + self.peer.how
+        if not self.fused_tail:
+            return "nccl:gradient larger than the fused kernel's limit"
+        try:
+            pb = parallel.PeerBuffer(self._grad_ext.numel(), self.device)
+        except Exception as e:        # noqa: BLE001
+            return "nccl:%s" % (str(e)[:120],)
+        self.peer = pb
+        self._grad_src = pb.local[: self._grad_ext.numel()]
+        self.peer_status = torch.zeros(1, device=self.device, dtype=torch.int32)
+        return "peer:" + pb.how
 
     @property
     def params(self) -> dict:
@@ -201,17 +230,19 @@ def clip_and_adam_torch_(flat, grad, mu, nu, step: int, lr, b1=0.9, b2=0.999, ep
     return gnorm
 
 
-def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch: Optional[int] = None,
-              loss: str = "l2"):
-    """Forward + VJP on this rank's shard, then the gradient all-reduce.  Leaves the reduced
-    gradient in ``state.grad`` and returns the (global) loss as a device scalar."""
+def _local_grad(state: TrainState, x: torch.Tensor, y: torch.Tensor, gb: int, loss: str):
+    """Forward + fused loss + VJP on this rank's shard: the local gradient and, behind it, the local loss term
+    land in ``state._grad_src``.  The forward also writes the gate it computes, so the backward does not
+    recompute it.  Returns the local loss (device scalar view)."""
     m = state.module
     dev = x.device
     centers, log_sigs = m._rbf_leaves(_unwrap(state.params), dev)
     v = state.views
     gd = m._gate_pack(dev)
-    gb = int(global_batch) if global_batch is not None else int(x.shape[0])
-    y_pred = ops.forward(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis)
+    B = int(x.shape[0])
+    if state.gate_buf is None or state.gate_buf.shape[0] != B:
+        state.gate_buf = torch.empty((B, m.num_regions), device=dev, dtype=torch.float32)
+    y_pred = ops.forward(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis, gate_out=state.gate_buf)
     if loss in DYNAMICS_LOSSES:
         terms, dy = ops.dynamics_loss(DYNAMICS_LOSSES[loss], x, y_pred, y, state.dyn_params, gb)
         state.loss_terms = terms          # [pred_loss, int_loss] of this shard (device)
@@ -219,10 +250,30 @@ def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch:
     else:
         lv, dy = ops.prediction_loss(y_pred, y, gb, loss)     # one launch; loss_and_cotangent is its torch spelling
         lval = lv[0]
-    ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gd=gd, basis=m._basis,
-                 grad_mask=state.mask, flat_out=state.grad)
+    n = state.grad.numel()
+    ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gate=state.gate_buf, basis=m._basis,
+                 grad_mask=state.mask, flat_out=state._grad_src[:n])
+    state._grad_src[n:n + 1].copy_(lval.reshape(1))      # the loss rides along: still one collective, no concat
+    return lval
+
+
+def _world():
+    import torch.distributed as dist
+    return dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+
+
+def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch: Optional[int] = None,
+              loss: str = "l2"):
+    """Forward + VJP on this rank's shard, then the gradient all-reduce.  Leaves the reduced
+    gradient in ``state.grad`` and returns the (global) loss as a device scalar."""
+    gb = int(global_batch) if global_batch is not None else int(x.shape[0])
+    lval = _local_grad(state, x, y, gb, loss)
+    n = state.grad.numel()
+    if state.peer is not None:
+        ops.fused_update_(None, None, None, state._grad_ext, n, 1, None, 0.0, peers=state.peer.ptrs,
+                          rank=state.peer.rank, world=state.peer.world, apply_update=False, status=state.peer_status)
+        return state._grad_ext[-1].clone()
     if gb != x.shape[0]:
-        state._grad_ext[-1:].copy_(lval.reshape(1))      # loss rides along: still one collective, no concat
         parallel.allreduce_sum_(state._grad_ext)
         lval = state._grad_ext[-1].clone()
     return lval
@@ -230,12 +281,25 @@ def grad_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch:
 
 def train_step(state: TrainState, x: torch.Tensor, y: torch.Tensor, global_batch: Optional[int] = None,
                loss: str = "l2"):
-    """One optimiser step (scripts/train_nmpc.py:258-300 without the dynamics term).  ``x``/``y``
-    are this rank's shard; ``global_batch`` the total over ranks.  Returns the loss (device scalar;
-    no host sync -- the reference's per-step wandb device_get is the caller's business)."""
-    lval = grad_step(state, x, y, global_batch, loss)
-    clip_and_adam_(state)
-    return lval
+    """One optimiser step (scripts/train_nmpc.py:258-300).  ``x``/``y`` are this rank's shard; ``global_batch``
+    the total over ranks.  Small gradients (every shipped NMPC shape) finish in ONE launch after the backward:
+    one-shot all-reduce over NVLink peer memory (if enabled) + clip + Adam; larger ones take the NCCL
+    all-reduce and the two-launch update.  Returns the loss (device scalar; no host sync -- the reference's
+    per-step wandb device_get is the caller's business)."""
+    gb = int(global_batch) if global_batch is not None else int(x.shape[0])
+    if not state.fused_tail or (state.peer is None and gb != x.shape[0] and _world() > 1):
+        lval = grad_step(state, x, y, global_batch, loss)
+        clip_and_adam_(state)
+        return lval
+    _local_grad(state, x, y, gb, loss)
+    n = state.grad.numel()
+    state.step += 1
+    pb = state.peer
+    ops.fused_update_(state.flat, state.mu, state.nu, state._grad_ext, n, 1, state.step_t.view(1), state.lr, state.b1,
+                      state.b2, state.eps, state.max_grad_norm, grad_norm=state.grad_norm,
+                      peers=pb.ptrs if pb is not None else None, rank=pb.rank if pb is not None else 0,
+                      world=pb.world if pb is not None else 1, apply_update=True, status=state.peer_status)
+    return state._grad_ext[-1].clone()
 
 
 class GraphedTrainStep:

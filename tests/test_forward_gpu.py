@@ -10,7 +10,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import golden_paths, load_golden, rel_max
+from conftest import golden_paths, load_golden, rel_l2, rel_max
 from oracle import irbfn_oracle as orc
 
 pytestmark = pytest.mark.gpu
@@ -272,3 +272,29 @@ def test_host_pipeline_variants_agree(cuda_device):
     torch.cuda.synchronize()
     assert torch.equal(yh, ref2)
     assert np.array_equal(net.apply_host(dp, x * 0.5, chunk=2048), ref2.numpy())
+
+
+def test_forward_also_writes_the_gate_for_the_backward(cuda_device):
+    """irbfn_forward_gate: same y as irbfn_forward, and the gate it writes is the tanh gate (model.py:70-95);
+    the backward fed with it as an external gate gives the parameter gradients of the descriptor form."""
+    ops = _ops()
+    dev = cuda_device
+    for path in [p for p in golden_paths() if "c2_frenet" in p or "warmstart_27" in p or "c1b" in p]:
+        cfg, params, arr = load_golden(path)
+        rb, lin = params["rbf_list"], params["linear"]
+        basis = orc.BASIS_IDS[cfg["basis_func"]]
+        x = _t(arr["x"], dev)
+        args = (x, _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(lin["kernel"], dev), _t(lin["bias"], dev))
+        gd = _gd(cfg, dev)
+        y0 = ops.forward(*args, gd=gd, basis=basis)
+        gate = torch.full((x.shape[0], cfg["num_regions"]), float("nan"), device=dev)
+        y1 = ops.forward(*args, gd=gd, basis=basis, gate_out=gate)
+        assert torch.equal(y0, y1)
+        ref = orc.region_activation(arr["x"].astype(np.float64), cfg["num_regions"], cfg["lower_bounds"],
+                                    cfg["upper_bounds"], cfg["delta"], cfg["dimension_ranges"])
+        assert np.abs(gate.cpu().numpy() - ref).max() <= 5e-6
+        dy = _t(np.random.default_rng(1).normal(size=arr["y64"].shape), dev)
+        ga = ops.backward(*args[:4], dy, gd=gd, basis=basis, grad_mask=ops.GRAD_PARAMS)
+        gb = ops.backward(*args[:4], dy, gate=gate, basis=basis, grad_mask=ops.GRAD_PARAMS)
+        for k in ("centers", "log_sigs", "kernel", "bias"):
+            assert rel_l2(gb[k].cpu().numpy(), ga[k].cpu().numpy()) < 1e-5, k

@@ -87,3 +87,35 @@ def test_clip_adam_is_deterministic_and_checks_arguments(cuda_device):
         ops.clip_adam_(p, g, mu, nu, torch.zeros(1, device=cuda_device), 1e-3)          # count must be float64
     with pytest.raises(Exception):
         ops.clip_adam_(p, g, mu, nu, cnt, 1e-3, b1=1.0)                                 # b1 outside [0, 1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,max_norm", [(1, 1.0), (11002, 1.0), (11002, 0.0), (131071, 1.0), (4097, 1e9)])
+def test_fused_single_launch_update_matches_oracle(n, max_norm, cuda_device):
+    """irbfn_fused_update without peers (one process): global norm + clip + Adam in ONE launch, against the
+    optax restatement and against the two-launch irbfn_clip_adam."""
+    from irbfn_b200 import ops
+    rng = np.random.default_rng(n)
+    p0 = rng.normal(size=n).astype(np.float32)
+    dev = cuda_device
+    p, mu, nu = torch.tensor(p0, device=dev), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    p2, mu2, nu2 = p.clone(), mu.clone(), nu.clone()
+    cnt, cnt2 = torch.zeros(1, device=dev, dtype=torch.float64), torch.zeros(1, device=dev, dtype=torch.float64)
+    gn = torch.zeros(1, device=dev)
+    rp, rmu, rnu, rc = p0.astype(np.float64), np.zeros(n), np.zeros(n), 0
+    for step in range(4):
+        g0 = (rng.normal(size=n) * (3.0 if step % 2 == 0 else 1e-3)).astype(np.float32)   # clipped / not clipped
+        g = torch.tensor(np.concatenate([g0, [7.5]]).astype(np.float32), device=dev)      # [grad | loss]
+        g2 = torch.tensor(g0, device=dev)
+        ops.fused_update_(p, mu, nu, g, n, 1, cnt, 1e-3, max_norm=max_norm, grad_norm=gn)
+        ops.clip_adam_(p2, g2, mu2, nu2, cnt2, 1e-3, max_norm=max_norm)
+        rp, rg, rmu, rnu, rc, rnorm = oo.adam_step(rp, g0.astype(np.float64), rmu, rnu, rc, lr=1e-3, max_norm=max_norm)
+        assert float(cnt) == step + 1 and float(g[n]) == 7.5             # the trailing float is left alone
+        assert abs(float(gn) - rnorm) <= 1e-5 * rnorm
+        assert _rel(g[:n].cpu().numpy(), rg) <= 2e-6                     # the gradient is clipped in place
+        assert _rel(p.cpu().numpy(), rp) <= 2e-6 and _rel(mu.cpu().numpy(), rmu) <= 2e-6
+        assert torch.allclose(p, p2, rtol=1e-6, atol=1e-7) and torch.allclose(nu, nu2, rtol=1e-5, atol=1e-12)
+    from irbfn_b200._lib import IrbfnError
+    with pytest.raises(IrbfnError):                                      # beyond the single-CTA limit
+        ops.fused_update_(None, None, None, torch.zeros((1 << 17) + 8, device=dev), (1 << 17) + 4, 1, None, 1e-3,
+                          apply_update=False)
