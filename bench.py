@@ -321,8 +321,14 @@ def main():
     elif not args.no_extras:
         extras(net, params, cfg, dev, world, args)   # collectives inside: every rank takes part
     if world > 1:
+        # every rank is done: leave without running destructors that talk to the (soon gone) process-group
+        # store -- torch symmetric-memory handles did hang dist.destroy_process_group() at exit on this pool
         import torch.distributed as dist
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def extras(net, params, cfg, dev, world, args):
@@ -359,26 +365,40 @@ def extras(net, params, cfg, dev, world, args):
     yall = torch.randn((GB, O), generator=g)
     x, y = xall[a:b].to(dev).contiguous(), yall[a:b].to(dev).contiguous()
     state = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+    # the gradient all-reduce: one-shot kernel over NVLink peer memory fused with clip + Adam when the node allows
+    # it (irbfn_fused_update); a second state keeps the plain NCCL path for comparison
+    how = state.enable_peer_allreduce()
     ms_g = timed(lambda: grad_step(state, x, y, GB), args.steps, args.warmup)
     ms_t = timed(lambda: train_step(state, x, y, GB), args.steps, args.warmup)
     from irbfn_b200.train import GraphedTrainStep
     gstep = GraphedTrainStep(state, x.shape[0], GB, loss="l2").load(x, y)
     ms_graph = timed(lambda: gstep(), args.steps, args.warmup)
+    ms_t_nccl = ms_graph_nccl = None
+    if how.startswith("peer"):
+        st_n = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+        ms_t_nccl = timed(lambda: train_step(st_n, x, y, GB), args.steps, args.warmup)
+        gstep_n = GraphedTrainStep(st_n, x.shape[0], GB, loss="l2").load(x, y)
+        ms_graph_nccl = timed(lambda: gstep_n(), args.steps, args.warmup)
+        del gstep_n, st_n
     # where the step's time goes: this rank's kernels alone (no collective: global batch = shard), the
-    # all-reduce of the flat gradient alone, and the rest (launch gaps, rank skew)
-    ms_local = timed(lambda: grad_step(state, x, y, x.shape[0]), args.steps, args.warmup)
-    ms_ar = timed(lambda: parallel.allreduce_sum_(state._grad_ext), args.steps, args.warmup) if world > 1 else 0.0
+    # NCCL all-reduce of the flat gradient alone, and the rest (launch gaps, rank skew)
+    st_l = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+    ms_local = timed(lambda: grad_step(st_l, x, y, x.shape[0]), args.steps, args.warmup)
+    ms_ar = timed(lambda: parallel.allreduce_sum_(st_l._grad_ext), args.steps, args.warmup) if world > 1 else 0.0
+    del st_l
     fl = R * K * (3 * D + 2) + 2 * K * O + R * K * (5 * D + 9) + 4 * K * O
     lane_step = R * K * (2 * D + 2) + K * O + R * K * (3 * D + 5) + 2 * K * O
     res["train_step_C3"] = {"global_batch": GB, "scaling": "strong", "ms_fwd_vjp_allreduce": ms_g,
                             "ms_with_clip_adam": ms_t, "ms_with_clip_adam_cuda_graph": ms_graph,
                             "samples_per_s": GB / (min(ms_t, ms_graph) * 1e-3),
                             "algorithmic_tflops": fl * GB / (ms_g * 1e-3) / 1e12,
-                            "allreduce_bytes": int(state._grad_ext.numel() * 4)}
+                            "allreduce_bytes": int(state._grad_ext.numel() * 4), "allreduce": how,
+                            "ms_with_clip_adam_nccl": ms_t_nccl, "ms_with_clip_adam_cuda_graph_nccl": ms_graph_nccl}
     tail["c3"] = {"shape": "R12_K100_D8_O2", "global_batch": GB, "n_gpus": world, "ms_eager": ms_t, "ms_graph": ms_graph,
-                  "ms_kernels_this_rank": ms_local, "ms_allreduce_alone": ms_ar,
+                  "allreduce": how, "ms_graph_nccl": ms_graph_nccl,
+                  "ms_kernels_this_rank": ms_local, "ms_nccl_allreduce_alone": ms_ar,
                   "ms_fwd_vjp_allreduce": ms_g, "allreduce_bytes": int(state._grad_ext.numel() * 4),
-                  "lane_ops_T_per_s": lane_step * GB / (ms_g * 1e-3) / 1e12}
+                  "lane_ops_T_per_s": lane_step * GB / (min(ms_t, ms_graph) * 1e-3) / 1e12}
 
     # 8(e) result check on hardware: the NCCL-reduced gradient of the sharded step against the gradient of
     # the whole batch on one device (rank 0 holds the full batch too); per-leaf ||g - g1|| / ||g1||
@@ -386,13 +406,15 @@ def extras(net, params, cfg, dev, world, args):
     torch.cuda.synchronize()
     if rank == 0:
         full = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+        full.flat.copy_(state.flat)       # the timed optimiser steps above moved the parameters
         if world > 1:
             grad_step(full, xall.to(dev), yall.to(dev), GB)
-            got, how = state, "NCCL all-reduce of %d shard gradients vs the full batch on rank 0" % world
+            got, how = state, "%s all-reduce of %d shard gradients vs the full batch on rank 0" % (how.split(":")[0], world)
         else:
             # one device: two half-batch shard gradients (means over the global batch) summed vs the full batch
             h = GB // 2
             halves = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+            halves.flat.copy_(state.flat)
             acc = torch.zeros_like(halves.grad)
             for lo_, hi_ in ((0, h), (h, GB)):
                 grad_step(halves, xall[lo_:hi_].to(dev), yall[lo_:hi_].to(dev), GB)   # world 1: the all-reduce is a no-op
@@ -497,6 +519,7 @@ def train_case(fixture, loss, GB, dev, rank, world, args, timed):
     x = (torch.rand((GB, D), generator=g) * torch.from_numpy(hi - lo) + torch.from_numpy(lo))[a:b].to(dev).contiguous()
     y = torch.randn((GB, O), generator=g)[a:b].to(dev).contiguous()
     state = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
+    how = state.enable_peer_allreduce()
     steps = max(3, args.steps // 2)
     ms_g = timed(lambda: grad_step(state, x, y, GB, loss), steps, 3)
     ms_t = timed(lambda: train_step(state, x, y, GB, loss), steps, 3)
@@ -506,7 +529,7 @@ def train_case(fixture, loss, GB, dev, rank, world, args, timed):
     return {"shape": "R%d_K%d_D%d_O%d" % (R, K, D, O), "loss": loss, "global_batch": GB, "n_gpus": world,
             "ms_eager": ms_t, "ms_graph": ms_graph, "ms_fwd_loss_vjp_allreduce": ms_g,
             "lane_ops_T_per_s": lane * GB / (ms_g * 1e-3) / 1e12,
-            "allreduce_bytes": int(state._grad_ext.numel() * 4)}
+            "allreduce_bytes": int(state._grad_ext.numel() * 4), "allreduce": how}
 
 
 def _fixture(name):

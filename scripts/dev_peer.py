@@ -81,4 +81,11 @@ if rank == 0:
                       "replicas_bit_identical": {"peer": id_peer, "nccl": id_nccl, "peer_after_graph": id_peer2},
                       "us_eager": {"nccl": t_eager_n, "peer": t_eager_p},
                       "us_graph": {"nccl": t_graph_n, "peer": t_graph_p}}), flush=True)
-dist.destroy_process_group()
+# teardown: symmetric-memory handles must go before the process group (their destructors talk to its store),
+# and a hard exit after the last barrier keeps a stuck destructor from hanging the job
+del gp, gn
+s_peer.peer = None
+torch.cuda.synchronize()
+dist.barrier()
+sys.stdout.flush()
+os._exit(0)
