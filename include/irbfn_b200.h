@@ -136,6 +136,25 @@ int irbfn_forward_gate(const float* x, const float* centers, const float* log_si
                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
 
 /*
+ * Gate-sparse, region-binned forward (tanh gate only).  Same result as irbfn_forward within
+ * an ABSOLUTE tolerance the caller chooses: a local network r is skipped for a query when
+ *     gamma_r <= tol_abs / (R * max_o sum_k |W[k,o]|),
+ * which bounds the dropped terms of model.py:187-196 by tol_abs per output (phi <= 1 for both bases), so
+ *     |y[b,o] - y_dense[b,o]| <= tol_abs  (+ fp32 rounding)   for every b, o.
+ * tol_abs = 0 skips only regions whose gate underflowed to exactly 0.  Queries are binned by their set of
+ * non-negligible gate intervals (a counting sort in the workspace) so that a warp's 128 queries skip the same
+ * regions; shapes whose parameters are staged in chunks stage only the regions a CTA needs.
+ *   counters   optional device uint64[2]: (warp, region-chunk, region) evaluations skipped / done
+ *   workspace  >= irbfn_forward_sparse_workspace_bytes(B, gd->num_bounds)
+ * B < 2^31.  The dense entry point stays the reference for timing and roofline accounting.
+ */
+size_t irbfn_forward_sparse_workspace_bytes(int64_t B, int num_bounds);
+int irbfn_forward_sparse(const float* x, const float* centers, const float* log_sigs, const float* W,
+                         const float* bias, const IrbfnGateDesc* gd, float* y, int64_t B, int R, int K,
+                         int D, int O, int basis, float tol_abs, uint64_t* counters, void* workspace,
+                         size_t workspace_bytes, irbfn_stream_t stream);
+
+/*
  * Backward (VJP).  Recomputes phi from x and the parameters; nothing from the forward is saved.
  *
  *   dy        (B,O)    cotangent of y, or NULL (then W may be NULL too)

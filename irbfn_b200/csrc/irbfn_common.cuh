@@ -80,18 +80,11 @@ __device__ __forceinline__ void load_queries4(const float* __restrict__ x, long 
 //     just loaded) instead of indexing the register copy, which would force the dimension loop to unroll
 //     into ~4,000 straight-line instructions executed once per tile (instruction-fetch stalls in ncu).
 //     Measured cost of the fused gate at C2: ~5 us of a 125 us tile (scripts/dev_gate_cost.py).
-__device__ __forceinline__ void gate_columns(const GateDev& gd, const float* __restrict__ x, long long q0,
-                                             long long B, int Dsrc, int r0, int rc, float4* gcol, int stride) {
+template <typename Load4>
+__device__ __forceinline__ void gate_columns_impl(const GateDev& gd, Load4 load4, int r0, int rc, float4* gcol,
+                                                  int stride) {
     const int S = gd.S;
     const int rlim = min(rc, gd.num_ranges - r0);
-    auto load4 = [&](int j) {
-        float4 v;
-        v.x = q0 + 0 < B ? __ldg(x + (q0 + 0) * Dsrc + j) : 0.f;
-        v.y = q0 + 1 < B ? __ldg(x + (q0 + 1) * Dsrc + j) : 0.f;
-        v.z = q0 + 2 < B ? __ldg(x + (q0 + 2) * Dsrc + j) : 0.f;
-        v.w = q0 + 3 < B ? __ldg(x + (q0 + 3) * Dsrc + j) : 0.f;
-        return v;
-    };
     auto factor = [&](const float4& v, float k2, int i) {
         const float lb = __ldg(gd.lower + i), ub = __ldg(gd.upper + i);
         float4 f;
@@ -139,6 +132,32 @@ __device__ __forceinline__ void gate_columns(const GateDev& gd, const float* __r
             }
         }
     }
+}
+
+// consecutive rows q0 .. q0+3
+__device__ __forceinline__ void gate_columns(const GateDev& gd, const float* __restrict__ x, long long q0,
+                                             long long B, int Dsrc, int r0, int rc, float4* gcol, int stride) {
+    gate_columns_impl(gd, [&](int j) {
+        float4 v;
+        v.x = q0 + 0 < B ? __ldg(x + (q0 + 0) * Dsrc + j) : 0.f;
+        v.y = q0 + 1 < B ? __ldg(x + (q0 + 1) * Dsrc + j) : 0.f;
+        v.z = q0 + 2 < B ? __ldg(x + (q0 + 2) * Dsrc + j) : 0.f;
+        v.w = q0 + 3 < B ? __ldg(x + (q0 + 3) * Dsrc + j) : 0.f;
+        return v;
+    }, r0, rc, gcol, stride);
+}
+// four arbitrary rows (a permuted batch); qi < 0 = no query
+__device__ __forceinline__ void gate_columns_rows(const GateDev& gd, const float* __restrict__ x,
+                                                  const long long (&qi)[4], int Dsrc, int r0, int rc, float4* gcol,
+                                                  int stride) {
+    gate_columns_impl(gd, [&](int j) {
+        float4 v;
+        v.x = qi[0] >= 0 ? __ldg(x + qi[0] * Dsrc + j) : 0.f;
+        v.y = qi[1] >= 0 ? __ldg(x + qi[1] * Dsrc + j) : 0.f;
+        v.z = qi[2] >= 0 ? __ldg(x + qi[2] * Dsrc + j) : 0.f;
+        v.w = qi[3] >= 0 ? __ldg(x + qi[3] * Dsrc + j) : 0.f;
+        return v;
+    }, r0, rc, gcol, stride);
 }
 
 // One thread per query, 256 per block: gamma (B,R) rows of the tanh gate.  Interval factors live in
@@ -196,6 +215,12 @@ struct FwdArgs {
     float* hidden;          // (B,K) or nullptr
     float* gate_out;        // (B,R) or nullptr: the fused tanh gate is also written out (training: the
                             // parameter-gradient kernel reads it instead of recomputing it)
+    // gate-sparse evaluation (SPARSE instantiation only): queries are visited in the order perm[0..B), which
+    // groups queries with the same set of non-negligible regions; a region whose gate is <= *gate_thr for all
+    // 128 queries of a warp is skipped by that warp
+    const int* perm;        // (B) or nullptr
+    const float* gate_thr;  // device scalar
+    unsigned long long* skip_count;   // optional: number of (warp, kernel-chunk, region) evaluations skipped / done
     long long B;
     int R, K;
     int Dsrc;               // features in memory (<= the kernel's compiled D; the rest is zero-padded)

@@ -271,6 +271,20 @@ class WCRBFNet(_IrbfnModule):
         return _IrbfnFunction.apply(xd, centers, log_sigs, kernel, bias, None, self._gate_pack(device),
                                     self._basis, False)
 
+    def apply_sparse(self, params, x, tol_abs: float, counters=None):
+        """``apply`` for inference sweeps with gate-sparse evaluation (irbfn_forward_sparse): local networks whose
+        gate cannot move any output by more than ``tol_abs`` in total are skipped, queries are binned so that
+        warps skip uniformly.  |result - apply(params, x)| <= tol_abs per output.  Not differentiable."""
+        device = self._device_of(x)
+        p = _unwrap(params)
+        xd = self._prep_x(x, device)
+        if xd is None:
+            xd = _leaf(x, device)
+        centers, log_sigs = self._rbf_leaves(p, device)
+        kernel, bias = _leaf(p["linear"]["kernel"], device), _leaf(p["linear"]["bias"], device)
+        return ops.forward_sparse(xd, centers, log_sigs, kernel, bias, gd=self._gate_pack(device), basis=self._basis,
+                                  tol_abs=tol_abs, counters=counters)
+
     def jacobian(self, params, x, with_value: bool = False):
         """jax.vmap(jax.jacrev(lambda q: self.apply(params, q[None])[0]))(x): (B, O, D), one pass
         (SURVEY.md 8f rank 2).  ``with_value`` also returns y (B, O) from the same launch."""

@@ -17,7 +17,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
                    GRAD_LOG_SIGS, GRAD_PARAMS, GRAD_X)
 
 __all__ = [
-    "GatePack", "forward", "backward", "region_gate", "softmax_gate", 
+    "GatePack", "forward", "forward_sparse", "backward", "region_gate", "softmax_gate", 
     "dynamics_loss", "integrate", "default_dyn_params", "jacobian", "fused_update_", "fused_update_max_n",
     "gather_rows", "GridKeys", "grid_index", "nearest_row",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
@@ -142,6 +142,40 @@ def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: Gate
     if want_y and want_hidden:
         return y, hidden
     return y if want_y else hidden
+
+
+def forward_sparse(x, centers, log_sigs, kernel, bias, *, gd: GatePack, basis: int = BASIS_GAUSSIAN,
+                   tol_abs: float = 0.0, out=None, counters=None):
+    """Gate-sparse, region-binned forward (irbfn_forward_sparse): y within ``tol_abs`` (absolute, per output) of
+    ``forward``.  ``counters``: optional int64 CUDA tensor of 2 elements receiving the number of (warp, region)
+    evaluations skipped / done."""
+    lib = _lib.load()
+    _chk(x, "x")
+    B, D = x.shape
+    _chk(centers, "centers")
+    R, K, Dc = centers.shape
+    if Dc != D:
+        raise ValueError("centers feature count %d != x feature count %d" % (Dc, D))
+    _chk(log_sigs, "log_sigs", (R, K))
+    O = kernel.shape[1]
+    _chk(kernel, "kernel", (K, O))
+    _chk(bias, "bias", (O,))
+    y = out if out is not None else torch.empty((B, O), device=x.device, dtype=torch.float32)
+    _chk(y, "out", (B, O))
+    if gd is None:
+        _lib.check(-5, "irbfn_forward_sparse")
+    if counters is not None and (counters.dtype != torch.int64 or counters.numel() != 2 or not counters.is_cuda):
+        raise ValueError("counters must be an int64 CUDA tensor with 2 elements")
+    if B == 0:
+        return y
+    with torch.cuda.device(x.device):
+        nbytes = lib.irbfn_forward_sparse_workspace_bytes(B, gd.desc.num_bounds)
+        ws = _workspace(nbytes, x.device)
+        rc = lib.irbfn_forward_sparse(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias), gd.ref(),
+                                      _ptr(y), B, R, K, D, O, basis, float(tol_abs), _ptr(counters), _ptr(ws), nbytes,
+                                      _stream())
+    _lib.check(rc, "irbfn_forward_sparse")
+    return y
 
 
 _ws_cache = {}

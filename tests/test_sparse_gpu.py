@@ -1,0 +1,96 @@
+"""Gate-sparse, region-binned forward (irbfn_forward_sparse) against the DENSE float64 oracle.
+
+The sparse path may drop a local network for a query only when its gate is below tol_abs / (R * max_o sum_k |W_ko|),
+so every output stays within tol_abs of the dense result; with the tolerances used here that keeps the norm-wise
+output error <= 1e-5 exactly like the dense kernel."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_paths, load_golden, rel_max
+from oracle import irbfn_oracle as orc
+from test_forward_gpu import SHAPES, _gd, _ops, _synthetic, _t
+
+pytestmark = pytest.mark.gpu
+WCRBF = [p for p in golden_paths() if "deeper" not in p and "cluster" not in p]
+
+
+@pytest.mark.parametrize("path", WCRBF, ids=[os.path.basename(p)[:-4] for p in WCRBF])
+def test_sparse_forward_matches_dense_oracle_on_shipped_checkpoints(path, cuda_device):
+    ops = _ops()
+    cfg, params, arr = load_golden(path)
+    rb, lin = params["rbf_list"], params["linear"]
+    dev = cuda_device
+    basis = orc.BASIS_IDS[cfg["basis_func"]]
+    args = (_t(arr["x"], dev), _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(lin["kernel"], dev), _t(lin["bias"], dev))
+    scale = np.abs(arr["y64"]).max()
+    cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+    y = ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=basis, tol_abs=1e-6 * scale, counters=cnt)
+    assert rel_max(y.cpu().numpy(), arr["y64"]) < 1e-5
+    skipped, done = (int(v) for v in cnt.cpu())
+    assert done > 0 and skipped >= 0
+    # tol_abs = 0 drops only gates that are exactly zero: the dense kernel's result to fp32 rounding
+    y0 = ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=basis, tol_abs=0.0)
+    yd = ops.forward(*args, gd=_gd(cfg, dev), basis=basis)
+    assert rel_max(y0.cpu().numpy(), arr["y64"]) < 1e-5
+    assert rel_max(y0.cpu().numpy(), yd.cpu().numpy()) < 1e-5      # (summation orders differ: split-K vs one pass)
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1, 1, 1), (1023, 3, 7, 4, 5), (5000, 4, 33, 6, 9), (4097, 12, 100, 8, 2),
+                                   (300, 70, 9, 5, 3), (2000, 130, 6, 7, 18)],
+                         ids=lambda s: "B%d_R%d_K%d_D%d_O%d" % s)
+def test_sparse_forward_ragged_shapes(shape, cuda_device):
+    ops = _ops()
+    B, R, K, D, O = shape
+    cfg, p, x = _synthetic(41, B, R, K, D, O, S=min(3, D), nb=(4, 3, 2))
+    cfg["delta"] = [40.0] * len(cfg["delta"])          # sharp gates: most regions are negligible for a query
+    dev = cuda_device
+    for basis, name in ((0, "gaussian"), (1, "inverse_quadratic")):
+        cfg["basis_func"] = name
+        params = {"rbf_list": {"centers": p["centers"], "log_sigs": p["log_sigs"]},
+                  "linear": {"kernel": p["kernel"], "bias": p["bias"]}}
+        ref = orc.wcrbf_forward(x.astype(np.float64), params, cfg)
+        args = (_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev), _t(p["bias"], dev))
+        tol = 1e-6 * np.abs(ref).max()
+        y = ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=basis, tol_abs=tol)
+        assert np.abs(y.cpu().numpy() - ref).max() <= 1e-5 * np.abs(ref).max()
+        y2 = ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=basis, tol_abs=tol)
+        assert torch.equal(y, y2)                      # the binning order cannot change a query's result
+
+
+def test_sparse_forward_on_the_stress_shape_skips_most_regions(cuda_device):
+    """C5-like: 64 non-overlapping regions (delta = 100), parameters larger than shared memory (chunked, compact
+    staging of the active regions only); random queries need the binning to skip uniformly."""
+    ops = _ops()
+    dev = cuda_device
+    R, K, D, O, B = 64, 512, 6, 16, 20000
+    rng = np.random.default_rng(7)
+    edges = np.linspace(-1.0, 1.0, 5)
+    cfg = dict(num_regions=R, lower_bounds=[list(edges[:-1])] * 3, upper_bounds=[list(edges[1:])] * 3, delta=[100.0] * 3,
+               dimension_ranges=[[i, j, k] for i in range(4) for j in range(4) for k in range(4)],
+               in_features=D, out_features=O, num_kernels=K, basis_func="gaussian", activation_idx=[0, 1, 2])
+    p = {"centers": rng.uniform(-1, 1, (R, K, D)).astype(np.float32), "log_sigs": rng.uniform(0, 2, (R, K)).astype(np.float32),
+         "kernel": rng.standard_normal((K, O)).astype(np.float32), "bias": np.zeros(O, np.float32)}
+    x = rng.uniform(-1, 1, (B, D)).astype(np.float32)
+    params = {"rbf_list": {"centers": p["centers"], "log_sigs": p["log_sigs"]}, "linear": {"kernel": p["kernel"], "bias": p["bias"]}}
+    ref = orc.wcrbf_forward(x.astype(np.float64), params, cfg, chunk=256)
+    cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+    y = ops.forward_sparse(_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev), _t(p["bias"], dev),
+                           gd=_gd(cfg, dev), basis=0, tol_abs=1e-6 * np.abs(ref).max(), counters=cnt)
+    assert np.abs(y.cpu().numpy() - ref).max() <= 1e-5 * np.abs(ref).max()
+    skipped, done = (int(v) for v in cnt.cpu())
+    assert skipped > 4 * done, (skipped, done)         # > 80 % of the (warp, region) evaluations skipped
+
+
+def test_sparse_forward_errors(cuda_device):
+    from irbfn_b200._lib import IrbfnError
+    ops = _ops()
+    cfg, p, x = _synthetic(3, 64, 2, 5, 4, 2)
+    dev = cuda_device
+    args = (_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev), _t(p["bias"], dev))
+    with pytest.raises(IrbfnError):
+        ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=0, tol_abs=-1.0)
+    with pytest.raises(IrbfnError):
+        ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=7, tol_abs=0.0)
