@@ -357,6 +357,28 @@ def extras(net, params, cfg, dev, world, args):
         torch.cuda.synchronize()
         return parallel.allreduce_max_scalar(e0.elapsed_time(e1) / steps, dev)
 
+    # gate-sparse, region-binned forward on the headline lattice: same queries, same parameters,
+    # every output within tol_abs of the dense kernel; the dense launch stays the headline and the roofline
+    xl = torch.from_numpy(lattice(cfg, vx_goal=4.0 + 0.25 * rank)).to(dev)
+    yd = ops.forward(xl, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"], p["linear"]["bias"],
+                     gd=net._gate_pack(dev), basis=0)
+    yscale = float(yd.abs().max())
+    cnt = torch.zeros(2, dtype=torch.int64, device=dev)
+    ysp = torch.empty_like(yd)
+    run_sp = lambda: ops.forward_sparse(xl, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
+                                        p["linear"]["bias"], gd=net._gate_pack(dev), basis=0, tol_abs=1e-6 * yscale,
+                                        out=ysp, counters=cnt)
+    ms_sp = timed(run_sp, args.steps, args.warmup)
+    ms_dn = timed(lambda: ops.forward(xl, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
+                                      p["linear"]["bias"], gd=net._gate_pack(dev), basis=0, out=yd), args.steps, args.warmup)
+    sk, dn = (int(v) for v in cnt.cpu())
+    res["forward_C2_gate_sparse"] = {"queries_per_gpu": B_LATTICE, "ms_sparse_incl_binning": ms_sp, "ms_dense": ms_dn,
+                                     "speedup": ms_dn / ms_sp, "tol_abs_over_max_abs_y": 1e-6,
+                                     "max_abs_diff_over_max_abs_y": float((ysp - yd).abs().max()) / yscale,
+                                     "skipped_fraction": sk / max(1, sk + dn),
+                                     "queries_per_s": world * B_LATTICE / (ms_sp * 1e-3)}
+    del xl, yd, ysp
+
     # C3: 262,144 samples per step in total (strong scaling: the global batch is fixed)
     GB = 262144
     a, b = parallel.shard_range(GB, rank, world)
@@ -625,6 +647,19 @@ def other_configs(dev, world, args, timed):
     res["forward_C5"] = {"queries_per_gpu": B5, "shape": "R64_K4096_D6_O16_gaussian", "ms": ms5,
                          "queries_per_s": world * B5 / (ms5 * 1e-3),
                          "lane_ops_T_per_s": lane5 * B5 / (ms5 * 1e-3) / 1e12, "timed_steps": 2, "warmup": 1}
+    # gate-sparse forward on the same 2^24 queries (delta = 100, non-overlapping regions: ~2 of 64 matter per query)
+    y5s = torch.empty_like(y5)
+    y5scale = float(y5.abs().max())
+    cnt5 = torch.zeros(2, dtype=torch.int64, device=dev)
+    ms5s = timed(lambda: ops.forward_sparse(x5, c5, ls5, W5, b5, gd=gd5, basis=0, tol_abs=1e-6 * y5scale, out=y5s,
+                                            counters=cnt5), 3, 1)
+    sk5, dn5 = (int(v) for v in cnt5.cpu())
+    res["forward_C5_gate_sparse"] = {"queries_per_gpu": B5, "ms_sparse_incl_binning": ms5s, "ms_dense": ms5,
+                                     "speedup": ms5 / ms5s, "tol_abs_over_max_abs_y": 1e-6,
+                                     "max_abs_diff_over_max_abs_y": float((y5s - y5).abs().max()) / y5scale,
+                                     "skipped_fraction": sk5 / max(1, sk5 + dn5),
+                                     "queries_per_s": world * B5 / (ms5s * 1e-3)}
+    del y5s
     B5b = 1 << 22
     dy5 = torch.randn((B5b, O), device=dev)
     flat = torch.empty(R * K * (D + 1) + K * O + O, device=dev)
@@ -636,6 +671,7 @@ def other_configs(dev, world, args, timed):
                                                / (ms5b * 1e-3) / 1e12, "timed_steps": 2, "warmup": 1}
     lane5b = lane5 + R * K * (3 * D + 5) + 2 * K * O
     res["c5_summary"] = {"shape": "R64_K4096_D6_O16", "n_gpus": world, "fwd_ms_per_2p24": ms5,
+                         "fwd_gate_sparse_ms_per_2p24": ms5s, "fwd_gate_sparse_skipped_fraction": sk5 / max(1, sk5 + dn5),
                          "fwd_lane_ops_T_per_s": lane5 * B5 / (ms5 * 1e-3) / 1e12,
                          "fwd_vjp_ms_per_2p22": ms5b, "fwd_vjp_lane_ops_T_per_s": lane5b * B5b / (ms5b * 1e-3) / 1e12}
     return res

@@ -221,6 +221,8 @@ struct FwdArgs {
     const int* perm;        // (B) or nullptr
     const float* gate_thr;  // device scalar
     unsigned long long* skip_count;   // optional: number of (warp, kernel-chunk, region) evaluations skipped / done
+    unsigned* work_counter; // SPARSE with resident parameters: warps fetch their next 128-query unit here (zeroed
+                            // by the caller): tiles differ 2-3x in active regions, a static split leaves a long tail
     long long B;
     int R, K;
     int Dsrc;               // features in memory (<= the kernel's compiled D; the rest is zero-padded)

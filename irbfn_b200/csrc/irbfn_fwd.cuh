@@ -71,8 +71,29 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
     const bool add_bias = blockIdx.y == 0;
     bool staged = false;
 
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        const long long q0 = (long long)tile * TQ + (long long)tid * Q;
+    // SPARSE with resident parameters: no barrier after the first staging, so every WARP schedules itself: its
+    // first 128-query unit is static (all warps meet in the staging barrier), the rest come from a counter.
+    const bool warp_sched = SPARSE && a.stage_once && a.work_counter != nullptr;
+    const long long num_units = (a.B + 32 * Q - 1) / (32 * Q);
+    long long iter = 0;
+    for (long long tile = blockIdx.x;; tile += gridDim.x, ++iter) {
+        long long q0;
+        if (warp_sched) {
+            long long u;
+            if (iter == 0) {
+                u = (long long)blockIdx.x * (NT / 32) + (tid >> 5);
+            } else {
+                unsigned v = 0;
+                if ((tid & 31) == 0) v = atomicAdd(a.work_counter, 1u);
+                v = __shfl_sync(0xffffffffu, v, 0);
+                u = (long long)gridDim.x * (NT / 32) + v;
+                if (u >= num_units) break;
+            }
+            q0 = u * (32 * Q) + (long long)(tid & 31) * Q;      // beyond B on the first round: an empty unit
+        } else {
+            if (tile >= a.num_tiles) break;
+            q0 = tile * TQ + (long long)tid * Q;
+        }
 
         // ---- queries -> registers, packed in pairs over queries ----
         float2 x2[2][D];

@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(256) sparse_scatter_kernel(const unsigned* __r
 }
 
 struct SparseLayout {
-    size_t thr_off, skip_off, hist_off, keys_off, perm_off, total;
+    size_t thr_off, skip_off, work_off, hist_off, keys_off, perm_off, total;
     int key_bits, nb;
 };
 
@@ -159,6 +159,7 @@ SparseLayout sparse_layout(int64_t B, int num_bounds) {
     size_t off = 0;
     L.thr_off = off; off = a256(off + sizeof(float));
     L.skip_off = off; off = a256(off + 2 * sizeof(unsigned long long));
+    L.work_off = off; off = a256(off + 8 * sizeof(unsigned));          // one work counter per output window
     L.hist_off = off; off = a256(off + (size_t)L.nb * sizeof(unsigned));
     L.keys_off = off; off = a256(off + (size_t)B * sizeof(unsigned));
     L.perm_off = off; off = a256(off + (size_t)B * sizeof(int));
@@ -245,6 +246,7 @@ extern "C" int irbfn_forward_sparse(const float* x, const float* centers, const 
         a.x = x; a.centers = centers; a.log_sigs = log_sigs; a.W = W; a.bias = bias;
         a.gate_ext = nullptr; a.gd = gdev; a.y = y; a.hidden = nullptr; a.gate_out = nullptr;
         a.perm = perm; a.gate_thr = thr; a.skip_count = o0 == 0 ? skip : nullptr;
+        a.work_counter = (o0 / 16 < 8) ? (unsigned*)(ws + L.work_off) + o0 / 16 : nullptr;
         a.B = B; a.R = R; a.K = K; a.Dsrc = D; a.ldw = O; a.o0 = o0; a.ocur = ocur;
         a.RC = plan.RC; a.KC = plan.KC; a.stage_once = plan.stage_once;
         const long long tq = (long long)plan.NT * FwdShape::Q;
