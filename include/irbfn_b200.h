@@ -340,7 +340,13 @@ int irbfn_gather_rows(const float* X, const float* Y, const int64_t* index, floa
  * irbfn_grid_index: per dimension d, index[b,d] = min(len_d - 1, searchsorted(keys_d, q[b,d],
  * side="right")) -- the grid lookup of ExplicitPlanner.plan (src/irbfn_mpc/explicit_planner.py:165-175).
  * keys: all dimensions' sorted key arrays concatenated; offset (num_dims + 1) int32 prefix sums;
- * q (B,num_dims); index (B,num_dims) int32.  Bit-exact with numpy.searchsorted (NaN sorts last).
+ * q (B,num_dims); index (B,num_dims) int32.  Index-exact with numpy.searchsorted on the SAME float32 keys and
+ * queries (NaN sorts last).  The reference bisects float64 table keys with float64 values: a value within
+ * float32 rounding of a key can land in the neighbouring cell once both are narrowed to float32 -- callers
+ * that need float64 cell boundaries pre-narrow their keys with nextafter towards the cell they want.
+ * irbfn_nearest_row compares float32 SQUARED distances with a strict <, rows in increasing order (lowest
+ * index wins exact ties of the squared distance); the reference takes argmin of float32 norms, where the
+ * square root can merge two distinct squared distances into one value and hand the tie to the lower index.
  */
 int irbfn_grid_index(const float* q, const float* keys, const int32_t* offset, int32_t* index,
                      int64_t B, int num_dims, irbfn_stream_t stream);

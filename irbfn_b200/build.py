@@ -99,11 +99,32 @@ def build(force: bool = False, verbose: bool = False) -> str:
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed for the peak probe:\n" + r.stderr[-4000:])
+    build_ffi(verbose)
     with open(stamp, "w") as f:
         f.write(digest)
     if verbose:
         print("built", LIB)
     return LIB
+
+
+def build_ffi(verbose: bool = False):
+    """The XLA FFI shim (ffi/irbfn_ffi.cc -> ffi/libirbfn_ffi.so) for the reference's JAX side.  It needs the XLA
+    FFI headers that ship with jaxlib; without JAX (this container, the GPU box) it is skipped -- the product and
+    its tests do not use it (irbfn_flax.py is the only consumer)."""
+    try:
+        import jax.ffi as jffi       # noqa: F401
+        inc = jffi.include_dir()
+    except Exception:
+        if verbose:
+            print("jax not importable: ffi/irbfn_ffi.cc not built (unverified source, see INTEGRATION.md)")
+        return None
+    out = os.path.join(HERE, "ffi", "libirbfn_ffi.so")
+    cmd = [_nvcc(), "-std=c++17", "-shared", "-Xcompiler", "-fPIC", "-I", inc, "-I", os.path.join(HERE, "..", "include"),
+           os.path.join(HERE, "ffi", "irbfn_ffi.cc"), "-L", HERE, "-lirbfn_b200", "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("irbfn_ffi.cc failed to build:\n" + r.stderr[-4000:])
+    return out
 
 
 if __name__ == "__main__":

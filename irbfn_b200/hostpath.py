@@ -18,7 +18,7 @@ class HostPipeline:
         self.device = torch.device(device)
         self.D, self.O, self.chunk = in_features, out_features, int(chunk)
         # Optionally cut each chunk's upload into `copy_streams` pieces on separate streams (separate DMA
-        # engines).  Measured on this pool (scripts/dev_h2d.py, dev_e2e.py): a lone 33.5 MB copy runs at
+        # engines).  Measured on this pool (scripts/dev_h2d.py): a lone 33.5 MB copy runs at
         # 25-55 GB/s depending on the box and two concurrent copies reach 55 GB/s, but inside the pipeline
         # the step is bound by the chunk kernels plus fill/drain, so 1 stream is the default.
         self.ncopy = max(1, int(copy_streams))
@@ -39,6 +39,7 @@ class HostPipeline:
         self.ev_out = [torch.cuda.Event() for _ in range(self.NBUF)]
         self._pin_in = None
         self._pin_out = None
+        self._pin_in_busy = None      # recorded after the last upload that reads _pin_in
         self._graphs, self._keep = {}, {}
 
     def _pinned_in(self, x):
@@ -47,6 +48,11 @@ class HostPipeline:
             return x
         t = torch.as_tensor(np.ascontiguousarray(np.asarray(x), dtype=np.float32)) if not isinstance(x, torch.Tensor) \
             else x.float().contiguous()
+        if self._pin_in_busy is not None:
+            # a previous call that returned without synchronising (caller-provided ``out``) may still be
+            # uploading from the staging buffer: do not overwrite it under the DMA engine
+            self._pin_in_busy.synchronize()
+            self._pin_in_busy = None
         if self._pin_in is None or self._pin_in.shape[0] < t.shape[0]:
             self._pin_in = torch.empty((t.shape[0], self.D), dtype=torch.float32).pin_memory()
         buf = self._pin_in[: t.shape[0]]
@@ -70,6 +76,10 @@ class HostPipeline:
             self._replay(xin, out, B, launch, graph_key)
         else:
             self._enqueue(xin, out, B, launch)
+        if self._pin_in is not None and xin.data_ptr() == self._pin_in.data_ptr():
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))     # the current stream waited for the pipeline's tail
+            self._pin_in_busy = ev
         if ret_numpy:
             torch.cuda.current_stream(self.device).synchronize()
             return out.numpy().copy()

@@ -26,7 +26,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .basis import basis_id
+from .basis import basis_id, log_sig_shift
 
 __all__ = ["WCRBFNet", "DeeperWCRBFNet", "ClusterWCRBFNet", "device_params"]
 
@@ -159,6 +159,7 @@ class _IrbfnModule:
         self.fixed_log_sigs = fixed_log_sigs
         self.num_split_dimensions = len(self.activation_idx)   # model.py:128 (F11: only the length)
         self._basis = basis_id(basis_func)                     # raises for unsupported functions
+        self._ls_shift = log_sig_shift(basis_func)             # gaussian_wide / gaussian_wider: width shift
         if self.in_features > ops._lib.MAX_D:
             raise ValueError("in_features %d exceeds the compiled maximum %d" % (in_features, ops._lib.MAX_D))
         if self.centers is not None:
@@ -208,6 +209,8 @@ class _IrbfnModule:
             if not self.fixed_width:
                 raise KeyError("params have no rbf_list/log_sigs and the module is not fixed_width")
             log_sigs = self._fixed("log_sigs", device)
+        if self._ls_shift != 0.0:
+            log_sigs = log_sigs + self._ls_shift     # gaussian_wide / _wider on the gaussian kernel (basis.py)
         return centers, log_sigs
 
     # ---- init: same tree, shapes and distributions as the reference -------------------------

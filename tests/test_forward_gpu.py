@@ -298,3 +298,31 @@ def test_forward_also_writes_the_gate_for_the_backward(cuda_device):
         gb = ops.backward(*args[:4], dy, gate=gate, basis=basis, grad_mask=ops.GRAD_PARAMS)
         for k in ("centers", "log_sigs", "kernel", "bias"):
             assert rel_l2(gb[k].cpu().numpy(), ga[k].cpu().numpy()) < 1e-5, k
+
+
+def test_gaussian_wide_and_wider_run_on_the_gaussian_kernel(cuda_device):
+    """flax_rbf.py:40-47: exp(-0.1 a^2), exp(-0.01 a^2) -- the gaussian kernel with shifted log-widths; checked
+    against the formula itself (float64), forward and log_sig gradient."""
+    from irbfn_b200 import basis as pbasis
+    from irbfn_b200.model import WCRBFNet, device_params
+    cfg, params, arr = load_golden([p for p in golden_paths() if "c2_frenet" in p][0])
+    x = arr["x"][:512].astype(np.float64)
+    rb, lin = params["rbf_list"], params["linear"]
+    gamma = orc.region_activation(x, cfg["num_regions"], cfg["lower_bounds"], cfg["upper_bounds"], cfg["delta"],
+                                  cfg["dimension_ranges"])
+    c, ls = rb["centers"].astype(np.float64), rb["log_sigs"].astype(np.float64)
+    alpha2 = ((x[:, None, None, :] - c[None]) ** 2).sum(-1) / np.exp(ls)[None] ** 2
+    for fn, coef in ((pbasis.gaussian_wide, 0.1), (pbasis.gaussian_wider, 0.01)):
+        phi = np.exp(-coef * alpha2)
+        ref = (gamma[:, :, None] * phi).sum(1) @ lin["kernel"].astype(np.float64) + lin["bias"].astype(np.float64)
+        net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], fn, cfg["num_regions"],
+                       cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"], cfg["delta"])
+        p = device_params({"params": params}, cuda_device)
+        p["params"]["rbf_list"]["log_sigs"].requires_grad_(True)
+        y = net.apply(p, torch.tensor(arr["x"][:512], device=cuda_device))
+        assert rel_max(y.detach().cpu().numpy(), ref) < 1e-5
+        (g,) = torch.autograd.grad((y ** 2).mean(), [p["params"]["rbf_list"]["log_sigs"]])
+        # d/d log_sig of exp(-coef a^2) = 2 coef a^2 phi
+        dh = (2 * ref / ref.size) @ lin["kernel"].astype(np.float64).T
+        gref = (dh[:, None, :] * gamma[:, :, None] * (2 * coef * alpha2 * phi)).sum(0)
+        assert rel_l2(g.cpu().numpy(), gref) < 1e-4

@@ -22,6 +22,14 @@ def test_basis_maps_by_name_and_rejects_undefined_functions():
     with pytest.raises(NotImplementedError):
         basis.basis_id(gaussian_narrow)
     a = np.linspace(0, 3, 7)
+    # gaussian_wide / gaussian_wider (flax_rbf.py:40-47) run on the gaussian kernel with shifted log-widths
+    assert basis.basis_id(basis.gaussian_wide) == _lib.BASIS_GAUSSIAN == basis.basis_id("gaussian_wider")
+    for fn, c in ((basis.gaussian_wide, 0.1), (basis.gaussian_wider, 0.01)):
+        np.testing.assert_allclose(fn(a), np.exp(-c * a ** 2))
+        ls = 0.3
+        d2 = a ** 2 * np.exp(2 * ls)                                   # alpha^2 = d^2 / sigma^2
+        np.testing.assert_allclose(np.exp(-c * a ** 2), np.exp(-d2 * np.exp(-2 * (ls + basis.log_sig_shift(fn)))), rtol=1e-12)
+    assert basis.log_sig_shift(basis.gaussian) == 0.0 == basis.log_sig_shift("inverse_quadratic")
     np.testing.assert_allclose(basis.gaussian(a), np.exp(-a ** 2))
     np.testing.assert_allclose(basis.inverse_quadratic(a), 1 / (1 + a ** 2))
 
