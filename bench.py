@@ -252,6 +252,23 @@ def main():
     ms_e2e = timed(lambda i: net.apply_host(params, xh, out=yh), args.steps, args.warmup)
     e2e = {"value": world * B / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
            "h2d_bytes_per_step": int(xh.numel() * 4), "d2h_bytes_per_step": int(yh.numel() * 4)}
+    # the same sweep through the lattice entry point: the queries are generated on the device from the axis
+    # values (a few hundred bytes up), the outputs still come down to pinned host memory every step.  Reported
+    # beside the generic host-buffer number, which stays the e2e headline.
+    lo_ = [min(b) for b in cfg["lower_bounds"]]
+    hi_ = [max(b) for b in cfg["upper_bounds"]]
+    axes_ = {c: np.linspace(lo_[c], hi_[c], n).astype(np.float32) for _, c, n in LATTICE}
+    fixed_ = np.zeros(8, np.float32)
+    fixed_[4], fixed_[7] = 4.0 + 0.25 * rank, 0.0
+
+    def lattice_step(i):
+        _, yl = net.apply_lattice(params, axes_, fixed_)
+        yh.copy_(yl, non_blocking=True)
+    ms_lat = timed(lattice_step, args.steps, args.warmup)
+    e2e["lattice_api"] = {"value": world * B / (ms_lat * 1e-3), "ms_per_step": ms_lat,
+                          "h2d_bytes_per_step": int(sum(v.size for v in axes_.values()) * 4 + 32 + 64),
+                          "d2h_bytes_per_step": int(yh.numel() * 4),
+                          "note": "WCRBFNet.apply_lattice: lattice built on the device (irbfn_lattice_queries)"}
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -337,6 +337,16 @@ int irbfn_gather_rows(const float* X, const float* Y, const int64_t* index, floa
                       int64_t n, int64_t N, int D, int O, int* bad_index_flag, irbfn_stream_t stream);
 
 /*
+ * irbfn_lattice_queries: the sweep's query lattice built on the device -- np.meshgrid(*axes, indexing="ij")
+ * over the listed columns, every other column held at fixed[col] (irbfn_vs_explicit_frenet.ipynb cell 8).
+ * values: the axes' values concatenated; offset (num_axes + 1) int32 prefix sums; column (num_axes) int32 query
+ * column of each axis (the first axis varies slowest); fixed (D); x (n, D) with n = product of the axis lengths.
+ * All device pointers.  Bit-exact with the NumPy spelling on the same float32 axis values.
+ */
+int irbfn_lattice_queries(const float* values, const int32_t* offset, const int32_t* column, int num_axes,
+                          const float* fixed, float* x, int64_t n, int D, irbfn_stream_t stream);
+
+/*
  * irbfn_grid_index: per dimension d, index[b,d] = min(len_d - 1, searchsorted(keys_d, q[b,d],
  * side="right")) -- the grid lookup of ExplicitPlanner.plan (src/irbfn_mpc/explicit_planner.py:165-175).
  * keys: all dimensions' sorted key arrays concatenated; offset (num_dims + 1) int32 prefix sums;

@@ -23,6 +23,11 @@ int launch_fwd_d5(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d6(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d7(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d8(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d4(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);   // gate-writing / gate-sparse variants
+int launch_fwdm_d5(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d6(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d7(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d8(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 
 // ---------------------------------------------------------------------------------------
 // device properties, cached per device (immutable after first query; benign race)
@@ -283,12 +288,22 @@ static int forward_impl(const float* x, const float* centers, const float* log_s
         a.num_tiles = (int)tiles;
         const int grid = (int)(tiles < dev.sms ? tiles : dev.sms);
         int e;
-        switch (DT) {
-            case 4: e = launch_fwd_d4(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            case 5: e = launch_fwd_d5(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            case 6: e = launch_fwd_d6(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            case 7: e = launch_fwd_d7(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            default: e = launch_fwd_d8(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+        if (a.gate_out != nullptr) {   // training forward: the variant that also writes the gate
+            switch (DT) {
+                case 4: e = launch_fwdm_d4(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                case 5: e = launch_fwdm_d5(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                case 6: e = launch_fwdm_d6(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                case 7: e = launch_fwdm_d7(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                default: e = launch_fwdm_d8(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            }
+        } else {
+            switch (DT) {
+                case 4: e = launch_fwd_d4(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                case 5: e = launch_fwd_d5(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                case 6: e = launch_fwd_d6(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                case 7: e = launch_fwd_d7(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+                default: e = launch_fwd_d8(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            }
         }
         if (e != 0) return note_cuda_error("irbfn_fwd_kernel", e);
         o0 += ocur;

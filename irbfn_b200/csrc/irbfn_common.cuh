@@ -80,6 +80,70 @@ __device__ __forceinline__ void load_queries4(const float* __restrict__ x, long 
 //     just loaded) instead of indexing the register copy, which would force the dimension loop to unroll
 //     into ~4,000 straight-line instructions executed once per tile (instruction-fetch stalls in ncu).
 //     Measured cost of the fused gate at C2: ~5 us of a 125 us tile (scripts/dev_gate_cost.py).
+__device__ __forceinline__ void gate_columns(const GateDev& gd, const float* __restrict__ x, long long q0,
+                                             long long B, int Dsrc, int r0, int rc, float4* gcol, int stride) {
+    const int S = gd.S;
+    const int rlim = min(rc, gd.num_ranges - r0);
+    auto load4 = [&](int j) {
+        float4 v;
+        v.x = q0 + 0 < B ? __ldg(x + (q0 + 0) * Dsrc + j) : 0.f;
+        v.y = q0 + 1 < B ? __ldg(x + (q0 + 1) * Dsrc + j) : 0.f;
+        v.z = q0 + 2 < B ? __ldg(x + (q0 + 2) * Dsrc + j) : 0.f;
+        v.w = q0 + 3 < B ? __ldg(x + (q0 + 3) * Dsrc + j) : 0.f;
+        return v;
+    };
+    auto factor = [&](const float4& v, float k2, int i) {
+        const float lb = __ldg(gd.lower + i), ub = __ldg(gd.upper + i);
+        float4 f;
+        f.x = gate_sigmoid(k2, v.x - lb) * gate_sigmoid(k2, ub - v.x);
+        f.y = gate_sigmoid(k2, v.y - lb) * gate_sigmoid(k2, ub - v.y);
+        f.z = gate_sigmoid(k2, v.z - lb) * gate_sigmoid(k2, ub - v.z);
+        f.w = gate_sigmoid(k2, v.w - lb) * gate_sigmoid(k2, ub - v.w);
+        return f;
+    };
+    float4 com = make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll 1
+    for (int j = 0; j < S; ++j) {
+        const int ob = __ldg(gd.offset + j), oe = __ldg(gd.offset + j + 1);
+        if (oe - ob == 1) {
+            const float4 f = factor(load4(j), 2.0f * kLog2e * __ldg(gd.delta + j), ob);
+            com.x *= f.x; com.y *= f.y; com.z *= f.z; com.w *= f.w;
+        }
+    }
+#pragma unroll 1
+    for (int rr = 0; rr < rc; ++rr) gcol[rr * stride] = rr < rlim ? com : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int j = 0; j < S; ++j) {
+        const int ob = __ldg(gd.offset + j), oe = __ldg(gd.offset + j + 1);
+        if (oe - ob > 1) {
+            const float k2 = 2.0f * kLog2e * __ldg(gd.delta + j);
+            const float4 v = load4(j);
+            const int* rg = gd.ranges + (size_t)r0 * S + j;
+#pragma unroll 1
+            for (int ib = ob; ib < oe; ib += 4) {
+                const float4 f0 = factor(v, k2, ib);
+                const float4 f1 = ib + 1 < oe ? factor(v, k2, ib + 1) : f0;
+                const float4 f2 = ib + 2 < oe ? factor(v, k2, ib + 2) : f0;
+                const float4 f3 = ib + 3 < oe ? factor(v, k2, ib + 3) : f0;
+#pragma unroll 2
+                for (int rr = 0; rr < rlim; ++rr) {
+                    const int idx = __ldg(rg + rr * S) - (ib - ob);
+                    if ((unsigned)idx < 4u) {
+                        const float4 lo = idx & 1 ? f1 : f0, hi = idx & 1 ? f3 : f2;
+                        const float4 f = idx & 2 ? hi : lo;
+                        float4 g = gcol[rr * stride];
+                        g.x *= f.x; g.y *= f.y; g.z *= f.z; g.w *= f.w;
+                        gcol[rr * stride] = g;
+                    }
+                }
+            }
+        }
+    }
+}
+
+// The same table for four ARBITRARY rows (gate-sparse forward: a permuted batch): identical arithmetic, the row
+// loader is a parameter.  (The consecutive-row version above is kept verbatim from round 1: routing it through
+// this template changed ptxas' schedule of the dense forward.)
 template <typename Load4>
 __device__ __forceinline__ void gate_columns_impl(const GateDev& gd, Load4 load4, int r0, int rc, float4* gcol,
                                                   int stride) {
@@ -134,18 +198,6 @@ __device__ __forceinline__ void gate_columns_impl(const GateDev& gd, Load4 load4
     }
 }
 
-// consecutive rows q0 .. q0+3
-__device__ __forceinline__ void gate_columns(const GateDev& gd, const float* __restrict__ x, long long q0,
-                                             long long B, int Dsrc, int r0, int rc, float4* gcol, int stride) {
-    gate_columns_impl(gd, [&](int j) {
-        float4 v;
-        v.x = q0 + 0 < B ? __ldg(x + (q0 + 0) * Dsrc + j) : 0.f;
-        v.y = q0 + 1 < B ? __ldg(x + (q0 + 1) * Dsrc + j) : 0.f;
-        v.z = q0 + 2 < B ? __ldg(x + (q0 + 2) * Dsrc + j) : 0.f;
-        v.w = q0 + 3 < B ? __ldg(x + (q0 + 3) * Dsrc + j) : 0.f;
-        return v;
-    }, r0, rc, gcol, stride);
-}
 // four arbitrary rows (a permuted batch); qi < 0 = no query
 __device__ __forceinline__ void gate_columns_rows(const GateDev& gd, const float* __restrict__ x,
                                                   const long long (&qi)[4], int Dsrc, int r0, int rc, float4* gcol,
@@ -213,16 +265,6 @@ struct FwdArgs {
     GateDev gd;
     float* y;               // (B,ldw) or nullptr
     float* hidden;          // (B,K) or nullptr
-    float* gate_out;        // (B,R) or nullptr: the fused tanh gate is also written out (training: the
-                            // parameter-gradient kernel reads it instead of recomputing it)
-    // gate-sparse evaluation (SPARSE instantiation only): queries are visited in the order perm[0..B), which
-    // groups queries with the same set of non-negligible regions; a region whose gate is <= *gate_thr for all
-    // 128 queries of a warp is skipped by that warp
-    const int* perm;        // (B) or nullptr
-    const float* gate_thr;  // device scalar
-    unsigned long long* skip_count;   // optional: number of (warp, kernel-chunk, region) evaluations skipped / done
-    unsigned* work_counter; // SPARSE with resident parameters: warps fetch their next 128-query unit here (zeroed
-                            // by the caller): tiles differ 2-3x in active regions, a static split leaves a long tail
     long long B;
     int R, K;
     int Dsrc;               // features in memory (<= the kernel's compiled D; the rest is zero-padded)
@@ -237,6 +279,18 @@ struct FwdArgs {
     int nsplit;             // gridDim.y
     int k_per_split;        // multiple of the kernel tile; >= K when gridDim.y == 1
     long long split_stride; // floats between partial outputs (0 when gridDim.y == 1)
+    // ---- only read by the irbfn_fwd_modes.cuh instantiations; kept BEHIND the round-1 fields so that the plain
+    // ---- dense kernel's parameter offsets (and with them its ptxas schedule) stay what they were
+    float* gate_out;        // (B,R) or nullptr: the fused tanh gate is also written out (training: the
+                            // parameter-gradient kernel reads it instead of recomputing it)
+    // gate-sparse evaluation (SPARSE instantiation only): queries are visited in the order perm[0..B), which
+    // groups queries with the same set of non-negligible regions; a region whose gate is <= *gate_thr for all
+    // 128 queries of a warp is skipped by that warp
+    const int* perm;        // (B) or nullptr
+    const float* gate_thr;  // device scalar
+    unsigned long long* skip_count;   // optional: number of (warp, kernel-chunk, region) evaluations skipped / done
+    unsigned* work_counter; // SPARSE with resident parameters: warps fetch their next 128-query unit here (zeroed
+                            // by the caller): tiles differ 2-3x in active regions, a static split leaves a long tail
 };
 
 // log-sigma -> the per-kernel scale used in the hot loop.

@@ -34,7 +34,7 @@ struct FwdShape {
     static __host__ __device__ constexpr int tile_floats(int D) { return (D + 1) * 4; }
 };
 
-template <int D, int OT, int BASIS, int NT, bool SPARSE = false>
+template <int D, int OT, int BASIS, int NT>
 __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
     constexpr int Q = FwdShape::Q, TQ = NT * Q, KT = FwdShape::KT;
     constexpr int OP = OT / 2;            // packed output pairs
@@ -48,19 +48,6 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
     float* gtab = Ws + (size_t)a.KC * (OT > 0 ? OT : 0);        // [RC][NT] float4
     float* stage = smem;
 
-    // gate-sparse evaluation: region masks of the current region chunk (<= 64 regions per chunk)
-    __shared__ unsigned long long s_cmask[3];   // union over the CTA's warps; three buffers in rotation so that
-                                                // re-zeroing one never races with a later chunk's atomicOr
-    __shared__ int s_slot2r[64];                // compact stage slot -> region of the chunk
-    float gthr = 0.f;
-    unsigned long long n_skip = 0, n_done = 0;
-    int parity = 0;
-    if (SPARSE) {
-        gthr = __ldg(a.gate_thr);
-        if (threadIdx.x < 3) s_cmask[threadIdx.x] = 0ull;
-        __syncthreads();
-    }
-
     const int tid = threadIdx.x;
     const int R = a.R, K = a.K, RC = a.RC, KC = a.KC;
     const int n_rch = (R + RC - 1) / RC;
@@ -71,47 +58,12 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
     const bool add_bias = blockIdx.y == 0;
     bool staged = false;
 
-    // SPARSE with resident parameters: no barrier after the first staging, so every WARP schedules itself: its
-    // first 128-query unit is static (all warps meet in the staging barrier), the rest come from a counter.
-    const bool warp_sched = SPARSE && a.stage_once && a.work_counter != nullptr;
-    const long long num_units = (a.B + 32 * Q - 1) / (32 * Q);
-    long long iter = 0;
-    for (long long tile = blockIdx.x;; tile += gridDim.x, ++iter) {
-        long long q0;
-        if (warp_sched) {
-            long long u;
-            if (iter == 0) {
-                u = (long long)blockIdx.x * (NT / 32) + (tid >> 5);
-            } else {
-                unsigned v = 0;
-                if ((tid & 31) == 0) v = atomicAdd(a.work_counter, 1u);
-                v = __shfl_sync(0xffffffffu, v, 0);
-                u = (long long)gridDim.x * (NT / 32) + v;
-                if (u >= num_units) break;
-            }
-            q0 = u * (32 * Q) + (long long)(tid & 31) * Q;      // beyond B on the first round: an empty unit
-        } else {
-            if (tile >= a.num_tiles) break;
-            q0 = tile * TQ + (long long)tid * Q;
-        }
+    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
+        const long long q0 = (long long)tile * TQ + (long long)tid * Q;
 
         // ---- queries -> registers, packed in pairs over queries ----
         float2 x2[2][D];
-        long long qi[Q];                     // SPARSE: the rows this thread evaluates (permuted order), -1 = none
-        if (SPARSE) {
-#pragma unroll
-            for (int i = 0; i < Q; ++i) qi[i] = q0 + i < a.B ? (long long)__ldg(a.perm + q0 + i) : -1ll;
-#pragma unroll
-            for (int p = 0; p < 2; ++p) {
-#pragma unroll
-                for (int j = 0; j < D; ++j) {
-                    x2[p][j].x = (qi[2 * p] >= 0 && j < a.Dsrc) ? __ldg(a.x + qi[2 * p] * a.Dsrc + j) : 0.f;
-                    x2[p][j].y = (qi[2 * p + 1] >= 0 && j < a.Dsrc) ? __ldg(a.x + qi[2 * p + 1] * a.Dsrc + j) : 0.f;
-                }
-            }
-        } else {
-            load_queries4<D>(a.x, q0, a.B, a.Dsrc, x2);
-        }
+        load_queries4<D>(a.x, q0, a.B, a.Dsrc, x2);
 
         // ---- output accumulators start at the bias ----
         float2 y2[Q][OPS];
@@ -141,59 +93,8 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
                     g.w = (q0 + 3 < a.B) ? __ldg(a.gate_ext + (q0 + 3) * R + r0 + rr) : 0.f;
                     gcol[rr * NT] = g;
                 }
-            } else if (SPARSE) {
-                gate_columns_rows(a.gd, a.x, qi, a.Dsrc, r0, rc, gcol, NT);
             } else {
                 gate_columns(a.gd, a.x, q0, a.B, a.Dsrc, r0, rc, gcol, NT);
-            }
-            // ---- SPARSE: which regions of the chunk matter to this warp / to the CTA ----
-            unsigned long long wmask = 0ull, cmask = 0ull;
-            if (SPARSE) {
-                for (int rr = 0; rr < rc; ++rr) {
-                    // the drop rule is applied PER QUERY (a gate at or below the threshold becomes 0), so a query's
-                    // result does not depend on which other queries share its warp; the warp then skips the
-                    // regions that are dropped for all of its queries
-                    float4 g = gcol[rr * NT];
-                    g.x = g.x > gthr ? g.x : 0.f;
-                    g.y = g.y > gthr ? g.y : 0.f;
-                    g.z = g.z > gthr ? g.z : 0.f;
-                    g.w = g.w > gthr ? g.w : 0.f;
-                    gcol[rr * NT] = g;
-                    const bool act = fmaxf(fmaxf(g.x, g.y), fmaxf(g.z, g.w)) > 0.f;
-                    if (__any_sync(0xffffffffu, act)) wmask |= 1ull << rr;
-                }
-                n_skip += (unsigned long long)(rc - __popcll(wmask));
-                n_done += (unsigned long long)__popcll(wmask);
-                if (!a.stage_once) {
-                    // parameters staged per (tile, chunk): the CTA stages only the regions some warp needs
-                    if ((tid & 31) == 0 && wmask) atomicOr(&s_cmask[parity], wmask);
-                    __syncthreads();
-                    cmask = s_cmask[parity];
-                    // buffer of the chunk after next: last read before this barrier, next written after the next one
-                    if (tid == 0) s_cmask[(parity + 2) % 3] = 0ull;
-                    parity = (parity + 1) % 3;
-                    if (cmask == 0ull) continue;            // CTA-uniform: nobody needs this region chunk
-                    if (tid < 64 && ((cmask >> tid) & 1ull)) s_slot2r[__popcll(cmask & ((1ull << tid) - 1ull))] = tid;
-                } else {
-                    cmask = ~0ull;      // everything is resident: warps skip on their own, no barrier per tile
-                }
-            }
-            const bool compact = SPARSE && !a.stage_once;     // stage only the CTA's active regions
-            const int n_stage_r = compact ? __popcll(cmask) : rc;
-            if (a.gate_out != nullptr && blockIdx.y == 0) {
-                // training: the gate goes out to (B,R) for the parameter-gradient kernel.  A warp owns 128
-                // consecutive queries, i.e. 128 * rc consecutive floats of the (B,R) rows when rc == R: its lanes
-                // copy them out of the warp's own table columns, coalesced (thread-private scattered 4-byte
-                // stores cost 40 % of the kernel; a CTA-wide copy needs two barriers per tile).
-                __syncwarp();
-                const int w0 = (tid >> 5) * 32;                         // first thread of this warp
-                const long long qw0 = (long long)tile * TQ + (long long)w0 * Q;
-                const int nq = (int)max(0ll, min((long long)(32 * Q), a.B - qw0));
-                for (int e = tid & 31; e < nq * rc; e += 32) {
-                    const int q = e / rc, rr = e - q * rc;
-                    a.gate_out[(qw0 + q) * R + r0 + rr] = gtab[((size_t)rr * NT + w0 + (q >> 2)) * 4 + (q & 3)];
-                }
-                __syncwarp();
             }
 
             for (int kch = 0; kch < n_kch; ++kch) {
@@ -203,11 +104,10 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
 
                 // ---- stage parameters of (region chunk, kernel chunk), transposed per 4-kernel tile ----
                 if (!(a.stage_once && staged)) {
-                    __syncthreads();  // everyone is done with the previous stage (and s_slot2r is visible)
-                    for (int idx = tid; idx < n_stage_r * kcp; idx += NT) {
-                        const int slot = idx / kcp, kk = idx - slot * kcp;
-                        const int rr = compact ? s_slot2r[slot] : slot;
-                        float* t = stage + ((size_t)slot * KCT + (kk >> 2)) * ((D + 1) * 4) + (kk & 3);
+                    __syncthreads();  // everyone is done with the previous stage
+                    for (int idx = tid; idx < rc * kcp; idx += NT) {
+                        const int rr = idx / kcp, kk = idx - rr * kcp;
+                        float* t = stage + ((size_t)rr * KCT + (kk >> 2)) * ((D + 1) * 4) + (kk & 3);
                         if (kk < kc) {
                             const size_t rk = (size_t)(r0 + rr) * K + (k0 + kk);
 #pragma unroll
@@ -332,46 +232,6 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
                 };
 
                 const size_t rstride = (size_t)KCT * (D + 1);
-                if (SPARSE) {
-                    // the same pipeline over the warp's active regions only (warp-uniform trip counts; the CTA's
-                    // barriers all sit in the staging above, which every warp still joins)
-                    if (wmask != 0ull) {
-                        const int rr0 = __ffsll((long long)wmask) - 1;
-                        const unsigned long long rest = wmask & (wmask - 1ull);
-                        const size_t slot0 = compact ? (size_t)__popcll(cmask & ((1ull << rr0) - 1ull)) : (size_t)rr0;
-                        for (int kt = 0; kt < kcp; kt += KT) {
-                            const float4* rec0 = stage4 + (size_t)(kt >> 2) * (D + 1);
-                            {   // first active region of the tile (peeled): also closes the previous kernel tile
-                                const float4* rec = rec0 + slot0 * rstride;
-                                const float4 g4 = gcol[rr0 * NT];
-                                float2 acc[KT][2];
-                                distances(rec, acc);
-                                blend();
-                                readout(kt > 0 ? kt - KT : 0);
-                                scale(rec, acc, g4);
-#pragma unroll
-                                for (int kk = 0; kk < KT; ++kk) h2[kk][0] = h2[kk][1] = make_float2(0.f, 0.f);
-                            }
-                            unsigned long long m = rest;
-                            while (m) {   // branch-free steady state over the other active regions
-                                const int rr = __ffsll((long long)m) - 1;
-                                m &= m - 1ull;
-                                const size_t slot = compact ? (size_t)__popcll(cmask & ((1ull << rr) - 1ull)) : (size_t)rr;
-                                const float4* rec = rec0 + slot * rstride;
-                                const float4 g4 = gcol[rr * NT];
-                                float2 acc[KT][2];
-                                distances(rec, acc);
-                                blend();
-                                scale(rec, acc, g4);
-                            }
-                        }
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) mufu(i);
-                        blend();
-                        readout(kcp - KT);
-                    }
-                    continue;
-                }
                 for (int kt = 0; kt < kcp; kt += KT) {
                     const float4* rec = stage4 + (size_t)(kt >> 2) * (D + 1);
                     {   // first region of the tile (peeled): also closes the previous kernel tile.
@@ -408,8 +268,8 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
         if (OT > 0) {
 #pragma unroll
             for (int q = 0; q < Q; ++q) {
-                const long long qq = SPARSE ? qi[q] : q0 + q;
-                if (SPARSE ? qq >= 0 : qq < a.B) {
+                const long long qq = q0 + q;
+                if (qq < a.B) {
                     float* yp = ybase + qq * a.ldw + a.o0;
 #pragma unroll
                     for (int op = 0; op < OP; ++op) {
@@ -420,16 +280,12 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_kernel(const FwdArgs a) {
             }
         }
     }
-    if (SPARSE && a.skip_count != nullptr && (tid & 31) == 0) {
-        atomicAdd(a.skip_count, n_skip);
-        atomicAdd(a.skip_count + 1, n_done);
-    }
 }
 
 // Host-side: pick the instantiation for (OT, basis, threads) and launch.  Returns a cudaError_t as int.
-template <int D, int OT, int BASIS, int NT, bool SPARSE = false>
+template <int D, int OT, int BASIS, int NT>
 inline int launch_fwd_inst(const FwdArgs& a, int grid, size_t smem, cudaStream_t st) {
-    auto kern = irbfn_fwd_kernel<D, OT, BASIS, NT, SPARSE>;
+    auto kern = irbfn_fwd_kernel<D, OT, BASIS, NT>;
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     kern<<<dim3(grid, a.nsplit > 0 ? a.nsplit : 1), NT, smem, st>>>(a);
@@ -439,11 +295,6 @@ inline int launch_fwd_inst(const FwdArgs& a, int grid, size_t smem, cudaStream_t
 template <int D, int OT>
 inline int launch_fwd_ot(const FwdArgs& a, int basis, int nt, int grid, size_t smem, cudaStream_t st) {
     if (nt != 256) return (int)cudaErrorInvalidValue;   // the one compiled CTA size (fwd_threads_for)
-    if (a.perm != nullptr) {                            // gate-sparse instantiation
-        if (OT == 0) return (int)cudaErrorInvalidValue;
-        if (basis == IRBFN_BASIS_GAUSSIAN) return launch_fwd_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 256, true>(a, grid, smem, st);
-        return launch_fwd_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 256, true>(a, grid, smem, st);
-    }
     if (basis == IRBFN_BASIS_GAUSSIAN) return launch_fwd_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 256>(a, grid, smem, st);
     return launch_fwd_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 256>(a, grid, smem, st);
 }

@@ -21,15 +21,15 @@
 #include <cuda_runtime.h>
 
 #include "irbfn_common.cuh"
-#include "irbfn_fwd.cuh"
+#include "irbfn_fwd.cuh"   // FwdShape
 #include "irbfn_plan.h"
 
 namespace irbfn {
-int launch_fwd_d4(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d5(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d6(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d7(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
-int launch_fwd_d8(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d4(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);   // irbfn_fwd_modes.cuh
+int launch_fwdm_d5(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d6(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d7(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwdm_d8(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int device_info(int* sms, int* smem_optin);                                       // irbfn_api.cu
 int check_gate(const float* gate, const IrbfnGateDesc* gd, int D, GateDev* out);  // irbfn_api.cu
 
@@ -255,11 +255,11 @@ extern "C" int irbfn_forward_sparse(const float* x, const float* centers, const 
         const int grid = (int)(tiles < sms ? tiles : sms);
         int e;
         switch (DT) {
-            case 4: e = launch_fwd_d4(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            case 5: e = launch_fwd_d5(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            case 6: e = launch_fwd_d6(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            case 7: e = launch_fwd_d7(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
-            default: e = launch_fwd_d8(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            case 4: e = launch_fwdm_d4(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            case 5: e = launch_fwdm_d5(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            case 6: e = launch_fwdm_d6(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            case 7: e = launch_fwdm_d7(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
+            default: e = launch_fwdm_d8(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
         }
         if (e != 0) return note_cuda_error("irbfn_fwd_kernel<sparse>", e);
         o0 += ocur;

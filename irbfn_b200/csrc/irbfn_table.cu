@@ -289,3 +289,58 @@ extern "C" int irbfn_nearest_row(const float* q, const float* table, int64_t* in
     e = (int)cudaGetLastError();
     return e != 0 ? note_cuda_error("nearest_row reduce", e) : IRBFN_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------------
+// Lattice queries on the device: the meshgrid of irbfn_vs_explicit_frenet.ipynb cell 8 (np.meshgrid(...,
+// indexing="ij") over some columns, the others held) written straight into HBM.  A 2^20-point sweep then
+// uploads a few hundred bytes of axis values instead of 33.5 MB of queries -- on an 8-GPU node the host link
+// (measured ~190 GB/s aggregate) is what bounds the host-buffer path.  HBM-bound: 4 D bytes per query.
+namespace irbfn {
+namespace {
+struct LatticeArgs {
+    const float* values;     // all axes' values concatenated
+    const int* offset;       // (naxes + 1) prefix sums into values
+    const int* column;       // (naxes) query column of each axis; the FIRST axis varies slowest
+    const float* fixed;      // (D) values of the columns no axis covers
+    float* x;                // (n, D)
+    long long n;
+    int naxes, D;
+};
+__global__ void __launch_bounds__(256) lattice_kernel(const LatticeArgs a) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < a.n; q += stride) {
+        float row[IRBFN_MAX_D];
+#pragma unroll
+        for (int j = 0; j < IRBFN_MAX_D; ++j) row[j] = j < a.D ? __ldg(a.fixed + j) : 0.f;
+        long long rem = q;
+        for (int i = a.naxes - 1; i >= 0; --i) {          // last axis varies fastest ("ij" order, C-contiguous)
+            const int lo = __ldg(a.offset + i), len = __ldg(a.offset + i + 1) - lo;
+            const int idx = (int)(rem % len);
+            rem /= len;
+            const float v = __ldg(a.values + lo + idx);
+            const int c = __ldg(a.column + i);
+#pragma unroll
+            for (int j = 0; j < IRBFN_MAX_D; ++j)
+                if (j == c) row[j] = v;
+        }
+#pragma unroll
+        for (int j = 0; j < IRBFN_MAX_D; ++j)
+            if (j < a.D) a.x[q * a.D + j] = row[j];
+    }
+}
+}  // namespace
+}  // namespace irbfn
+
+extern "C" int irbfn_lattice_queries(const float* values, const int32_t* offset, const int32_t* column, int num_axes,
+                                     const float* fixed, float* x, int64_t n, int D, irbfn_stream_t stream) {
+    if (n < 0 || D <= 0 || num_axes < 0) return IRBFN_ERR_BAD_DIMS;
+    if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
+    if (n == 0) return IRBFN_OK;
+    if (!fixed || !x || (num_axes > 0 && (!values || !offset || !column))) return IRBFN_ERR_NULL_POINTER;
+    irbfn::LatticeArgs a{values, offset, column, fixed, x, n, num_axes, D};
+    const long long nb = (n + 255) / 256;
+    irbfn::lattice_kernel<<<(unsigned)(nb < 148 * 16 ? nb : 148 * 16), 256, 0, (cudaStream_t)stream>>>(a);
+    const int e = (int)cudaGetLastError();
+    return e != 0 ? irbfn::note_cuda_error("lattice_kernel", e) : IRBFN_OK;
+}

@@ -274,6 +274,16 @@ class WCRBFNet(_IrbfnModule):
         return _IrbfnFunction.apply(xd, centers, log_sigs, kernel, bias, None, self._gate_pack(device),
                                     self._basis, False)
 
+    def apply_lattice(self, params, axes, fixed, tol_abs: Optional[float] = None):
+        """The sweep of irbfn_vs_explicit*.ipynb cells 8-10 without moving the lattice over the host link:
+        queries = meshgrid(axes, indexing="ij") with the other columns held at ``fixed``, generated on the device
+        (``ops.lattice_queries``), then ``apply`` (or ``apply_sparse`` when ``tol_abs`` is given).
+        Returns (x, y), both CUDA tensors."""
+        device = _default_device()
+        x = ops.lattice_queries(axes, fixed, device)
+        y = self.apply(params, x) if tol_abs is None else self.apply_sparse(params, x, tol_abs)
+        return x, y
+
     def apply_sparse(self, params, x, tol_abs: float, counters=None):
         """``apply`` for inference sweeps with gate-sparse evaluation (irbfn_forward_sparse): local networks whose
         gate cannot move any output by more than ``tol_abs`` in total are skipped, queries are binned so that

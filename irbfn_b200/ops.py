@@ -18,7 +18,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
 
 __all__ = [
     "GatePack", "forward", "forward_sparse", "backward", "region_gate", "softmax_gate", 
-    "dynamics_loss", "integrate", "default_dyn_params", "jacobian", "fused_update_", "fused_update_max_n",
+    "dynamics_loss", "integrate", "default_dyn_params", "jacobian", "fused_update_", "fused_update_max_n", "lattice_queries",
     "gather_rows", "GridKeys", "grid_index", "nearest_row",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
     "GRAD_X", "GRAD_GATE", "GRAD_PARAMS",
@@ -365,6 +365,30 @@ def clip_adam_(params, grad, mu, nu, step_count, lr: float, b1: float = 0.9, b2:
                                  max_norm, _ptr(grad_norm), _ptr(ws), nbytes, _stream())
     _lib.check(rc, "irbfn_clip_adam")
     return grad_norm
+
+
+def lattice_queries(axes, fixed, device=None):
+    """(prod n_i, D) fp32 CUDA tensor: np.meshgrid(*axes.values(), indexing="ij") over the columns that are the
+    keys of ``axes`` (insertion order, first varies slowest), the other columns held at ``fixed`` -- built on the
+    device by irbfn_lattice_queries from a few hundred bytes of axis values."""
+    import numpy as np
+    lib = _lib.load()
+    device = torch.device(device if device is not None else "cuda")
+    cols = [int(c) for c in axes.keys()]
+    vals = [np.asarray(axes[c], np.float32).ravel() for c in axes.keys()]
+    D = len(fixed)
+    if any(c < 0 or c >= D for c in cols) or len(set(cols)) != len(cols):
+        raise ValueError("axis columns must be distinct and inside [0, %d)" % D)
+    n = int(np.prod([len(v) for v in vals])) if vals else 1
+    off = np.cumsum([0] + [len(v) for v in vals]).astype(np.int32)
+    v_d = torch.from_numpy(np.concatenate(vals) if vals else np.zeros(1, np.float32)).to(device)
+    o_d, c_d = torch.from_numpy(off).to(device), torch.from_numpy(np.asarray(cols or [0], np.int32)).to(device)
+    f_d = torch.from_numpy(np.asarray(fixed, np.float32)).to(device)
+    x = torch.empty((n, D), device=device, dtype=torch.float32)
+    with torch.cuda.device(device):
+        rc = lib.irbfn_lattice_queries(_ptr(v_d), _ptr(o_d), _ptr(c_d), len(cols), _ptr(f_d), _ptr(x), n, D, _stream())
+    _lib.check(rc, "irbfn_lattice_queries")
+    return x
 
 
 def fused_update_max_n() -> int:

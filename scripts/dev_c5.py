@@ -23,3 +23,12 @@ e0.record()
 ops.backward(x, c, ls, W, dy, gd=gd, basis=0, grad_mask=ops.GRAD_PARAMS, flat_out=flat)
 e1.record(); torch.cuda.synchronize()
 print("B", B, "backward ms", e0.elapsed_time(e1))
+y = torch.empty((B, O), device=dev)
+b0 = torch.zeros(O, device=dev)
+for _ in range(2):
+    ops.forward(x, c, ls, W, b0, gd=gd, basis=0, out=y)
+torch.cuda.synchronize()
+e0.record()
+ops.forward(x, c, ls, W, b0, gd=gd, basis=0, out=y)
+e1.record(); torch.cuda.synchronize()
+print("B", B, "forward ms", e0.elapsed_time(e1))

@@ -139,3 +139,17 @@ def test_table_errors(cuda_device):
         ops.gather_rows(q, None, torch.zeros(3, device=cuda_device, dtype=torch.int32))
     with pytest.raises(ValueError):
         ops.grid_index(q, ops.GridKeys([[0.0, 1.0]], cuda_device))
+
+
+def test_lattice_queries_match_the_numpy_meshgrid(cuda_device):
+    """irbfn_lattice_queries against irbfn_b200.sweep.lattice_queries (NumPy, the notebook's spelling): bit-exact."""
+    from irbfn_b200 import ops
+    from irbfn_b200.sweep import lattice_queries
+    rng = np.random.default_rng(0)
+    for D, axes in ((8, {0: np.linspace(-0.2, 2.2, 7), 6: np.linspace(-1, 1, 5), 2: np.linspace(1, 7, 3)}),
+                    (5, {4: rng.normal(size=11)}), (3, {}), (8, {c: rng.normal(size=n) for c, n in zip(range(8), (2, 3, 2, 5, 2, 3, 2, 2))})):
+        axes = {c: np.asarray(v, np.float32) for c, v in axes.items()}
+        fixed = rng.normal(size=D).astype(np.float32)
+        ref = lattice_queries(axes, fixed)
+        got = ops.lattice_queries(axes, fixed, cuda_device).cpu().numpy()
+        assert got.shape == ref.shape and np.array_equal(got, ref)
