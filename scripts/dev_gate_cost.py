@@ -21,7 +21,6 @@ for B in (131072, 1 << 20):
     x = torch.rand((B, 8), device=dev)
     g = ops.region_gate(x, gd, 12)
     y = torch.empty((B, 2), device=dev)
-    os.environ["IRBFN_DEV_KPS"] = "100"
     t_f = timed(lambda: ops.forward(x, c, ls, W, b, gd=gd, basis=0, out=y))
     t_e = timed(lambda: ops.forward(x, c, ls, W, b, gate=g, basis=0, out=y))
     t_g = timed(lambda: ops.region_gate(x, gd, 12))

@@ -1,0 +1,15 @@
+#!/bin/bash
+# Round-2 verification on one B200 (run under gpurun): GPU tests, smoke, both bench arms, launch list,
+# one full ncu capture of the headline forward.  usage: scripts/verify_r2.sh <tag>
+set -u
+TAG=${1:-r2}
+O=gpurun_out
+python -m pytest tests -m gpu -x -q 2>&1 | tail -5 > $O/pytest_gpu_${TAG}.log
+python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke_${TAG}.log 2>&1; echo smoke=$? >> $O/smoke_${TAG}.log
+python bench.py > $O/bench_${TAG}_n1.json 2> $O/bench_${TAG}_n1.err
+python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_${TAG}_reference.json 2> $O/bench_${TAG}_ref.err
+CMD="python bench.py --steps 2 --warmup 3 --no-cpu"
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/launches_${TAG}.csv $CMD > $O/ncu_launches_${TAG}.log 2>&1
+bash scripts/profile_fwd.sh ${TAG}
+tail -n 3 $O/pytest_gpu_${TAG}.log $O/smoke_${TAG}.log
+cut -c1-600 $O/bench_${TAG}_n1.json; cut -c1-400 $O/bench_${TAG}_reference.json

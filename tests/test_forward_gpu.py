@@ -326,3 +326,56 @@ def test_gaussian_wide_and_wider_run_on_the_gaussian_kernel(cuda_device):
         dh = (2 * ref / ref.size) @ lin["kernel"].astype(np.float64).T
         gref = (dh[:, None, :] * gamma[:, :, None] * (2 * coef * alpha2 * phi)).sum(0)
         assert rel_l2(g.cpu().numpy(), gref) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------
+# Large batches: the persistent kernel walks several 1,024-query tiles per CTA.  A query's result must not depend on
+# which tile / CTA / call it was evaluated in: one call over the whole batch against the same batch evaluated in pieces
+# of 64 tiles (those take the split-over-kernels path, whose partial sums are added in another order, hence a rounding
+# tolerance rather than bit equality) -- and against the float64 oracle on a sample that includes the ragged tail.
+# ---------------------------------------------------------------------------------------------------
+def _big_queries(arr, n, dev, seed):
+    """n queries spread over (and a little beyond) the fixture's own input range."""
+    x0 = arr["x"].astype(np.float32)
+    lo, hi = x0.min(0), x0.max(0)
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    u = torch.rand((n, x0.shape[1]), generator=g, dtype=torch.float32)
+    x = torch.tensor(lo) + u * torch.tensor((hi - lo) * 1.1 + 1e-3) - torch.tensor((hi - lo) * 0.05)
+    return x.to(dev).contiguous()
+
+
+@pytest.mark.parametrize("name", ["c2_frenet_12x100", "c1_cartesian_1x1000", "dnmpc_4regions_iq",
+                                  "c2b_frenet_1x1000_o10", "cluster_500x10", "dnmpc_9regions_multiv"])
+def test_large_batch_equals_piecewise_evaluation_and_oracle(name, cuda_device):
+    ops = _ops()
+    path = [p for p in golden_paths() if os.path.basename(p)[:-4] == name][0]
+    cfg, params, arr = load_golden(path)
+    dev = cuda_device
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    n = 2 * sms * 1024 + 777                       # ragged last tile, two tiles and a bit per SM
+    x = _big_queries(arr, n, dev, 11)
+    rb = params["rbf_list"]
+    basis = orc.BASIS_IDS[cfg["basis_func"]]
+    args = (_t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(params["linear"]["kernel"], dev),
+            _t(params["linear"]["bias"], dev))
+    if cfg["kind"] == "cluster":
+        gate, _ = ops.softmax_gate(x, _t(params["cluster"]["kernel"], dev), _t(params["cluster"]["bias"], dev))
+        run = lambda lo, hi: ops.forward(x[lo:hi], *args, gate=gate[lo:hi].contiguous(), basis=basis)
+    else:
+        gd = _gd(cfg, dev)
+        run = lambda lo, hi: ops.forward(x[lo:hi], *args, gd=gd, basis=basis)
+    y = run(0, n)
+    step = 65536                                   # 64 tiles per piece
+    y_plain = torch.cat([run(lo, min(n, lo + step)) for lo in range(0, n, step)])
+    assert rel_max(y.cpu().numpy(), y_plain.cpu().numpy().astype(np.float64)) < 2e-6
+    # against the float64 oracle on a strided sample (including the ragged tail)
+    idx = np.unique(np.concatenate([np.arange(0, n, 97), np.arange(n - 800, n)]))
+    xs = x[torch.tensor(idx, device=dev)].cpu().numpy().astype(np.float64)
+    if cfg["kind"] == "cluster":
+        y_ref, _ = orc.cluster_forward(xs, params, cfg)
+    else:
+        gamma = orc.region_activation(xs, cfg["num_regions"], cfg["lower_bounds"], cfg["upper_bounds"], cfg["delta"],
+                                      cfg["dimension_ranges"])
+        y_ref = orc.forward(xs, rb["centers"], rb["log_sigs"], params["linear"]["kernel"], params["linear"]["bias"],
+                            gamma, basis)
+    assert rel_max(y[torch.tensor(idx, device=dev)].cpu().numpy(), y_ref) < OUT_TOL
