@@ -330,9 +330,10 @@ def test_gaussian_wide_and_wider_run_on_the_gaussian_kernel(cuda_device):
 
 # ---------------------------------------------------------------------------------------------------
 # Large batches: the persistent kernel walks several 1,024-query tiles per CTA.  A query's result must not depend on
-# which tile / CTA / call it was evaluated in: one call over the whole batch against the same batch evaluated in pieces
-# of 64 tiles (those take the split-over-kernels path, whose partial sums are added in another order, hence a rounding
-# tolerance rather than bit equality) -- and against the float64 oracle on a sample that includes the ragged tail.
+# which tile / CTA / call it was evaluated in: one call over the whole batch must agree BIT FOR BIT with the same batch
+# evaluated in pieces of 64 tiles (split=False: the same unsplit kernel, so the same order of additions), within
+# rounding with the pieces' default split-over-kernels path, and with the float64 oracle on a sample that includes the
+# ragged tail.
 # ---------------------------------------------------------------------------------------------------
 def _big_queries(arr, n, dev, seed):
     """n queries spread over (and a little beyond) the fixture's own input range."""
@@ -360,14 +361,17 @@ def test_large_batch_equals_piecewise_evaluation_and_oracle(name, cuda_device):
             _t(params["linear"]["bias"], dev))
     if cfg["kind"] == "cluster":
         gate, _ = ops.softmax_gate(x, _t(params["cluster"]["kernel"], dev), _t(params["cluster"]["bias"], dev))
-        run = lambda lo, hi: ops.forward(x[lo:hi], *args, gate=gate[lo:hi].contiguous(), basis=basis)
+        run = lambda lo, hi, **kw: ops.forward(x[lo:hi], *args, gate=gate[lo:hi].contiguous(), basis=basis, **kw)
     else:
         gd = _gd(cfg, dev)
-        run = lambda lo, hi: ops.forward(x[lo:hi], *args, gd=gd, basis=basis)
-    y = run(0, n)
+        run = lambda lo, hi, **kw: ops.forward(x[lo:hi], *args, gd=gd, basis=basis, **kw)
+    y = run(0, n, split=False)
+    assert rel_max(run(0, n).cpu().numpy(), y.cpu().numpy().astype(np.float64)) < OUT_TOL   # the default call
     step = 65536                                   # 64 tiles per piece
-    y_plain = torch.cat([run(lo, min(n, lo + step)) for lo in range(0, n, step)])
-    assert rel_max(y.cpu().numpy(), y_plain.cpu().numpy().astype(np.float64)) < 2e-6
+    y_plain = torch.cat([run(lo, min(n, lo + step), split=False) for lo in range(0, n, step)])
+    assert torch.equal(y, y_plain)
+    y_split = torch.cat([run(lo, min(n, lo + step)) for lo in range(0, n, step)])
+    assert rel_max(y_split.cpu().numpy(), y.cpu().numpy().astype(np.float64)) < OUT_TOL
     # against the float64 oracle on a strided sample (including the ragged tail)
     idx = np.unique(np.concatenate([np.arange(0, n, 97), np.arange(n - 800, n)]))
     xs = x[torch.tensor(idx, device=dev)].cpu().numpy().astype(np.float64)
