@@ -136,6 +136,27 @@ int irbfn_forward_gate(const float* x, const float* centers, const float* log_si
                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
 
 /*
+ * irbfn_forward for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ *
+ * Same arguments and result as irbfn_forward without the workspace pair.  The split-over-kernels partial outputs of
+ * small batches (what irbfn_forward_workspace_bytes sizes) go to a file-scope `static __device__` array of
+ * IRBFN_NOALLOC_SCRATCH_BYTES (8 MiB) inside the library; every GPU that loads the library holds those 8 MiB until the
+ * process exits.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine), on any call.
+ *   - IRBFN_ERR_WORKSPACE (irbfn_last_error_detail() names both sizes) when irbfn_forward_workspace_bytes(B, ...)
+ *     exceeds IRBFN_NOALLOC_SCRATCH_BYTES: use irbfn_forward with a caller-owned workspace, or a smaller batch.
+ *     (Batches of >= 4 tiles of 1,024 queries per SM need no scratch at all and always pass.)
+ *   - every call on a device shares the one array and it keeps the last call's contents.  Nothing in it has to start
+ *     at zero: each split writes its whole partial output before the fixed-order reduction reads it.  Calls that
+ *     OVERLAP on the GPU (different streams, or replays of graphs that captured it) RACE on the array: serialise them.
+ */
+#define IRBFN_NOALLOC_SCRATCH_BYTES (8u << 20)
+int irbfn_forward_noalloc(const float* x, const float* centers, const float* log_sigs, const float* W,
+                          const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
+                          float* hidden, int64_t B, int R, int K, int D, int O, int basis,
+                          irbfn_stream_t stream);
+
+/*
  * Gate-sparse, region-binned forward (tanh gate only).  Same result as irbfn_forward within
  * an ABSOLUTE tolerance the caller chooses: a local network r is skipped for a query when
  *     gamma_r <= tol_abs / (R * max_o sum_k |W[k,o]|),

@@ -158,6 +158,36 @@ __global__ void __launch_bounds__(256) split_reduce_kernel(const float* __restri
 
 using namespace irbfn;
 
+// ---------------------------------------------------------------------------------------
+// irbfn_forward_noalloc: scratch for the split-over-kernels partial outputs lives in the library image.
+// In HOST code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the address is
+// looked up once per device, with that device current, by cudaGetSymbolAddress (no allocation: the array is
+// part of the module's global segment).
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[IRBFN_NOALLOC_SCRATCH_BYTES];
+
+static int noalloc_scratch_address(void** out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) {
+        cudaGetLastError();
+        return IRBFN_ERR_NO_DEVICE;
+    }
+    static void* cache[64];   // immutable per device after the first lookup; benign race (same value)
+    if (dev < 64 && cache[dev] != nullptr) {
+        *out = cache[dev];
+        return IRBFN_OK;
+    }
+    void* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+        cudaGetLastError();
+        return note_cuda_error("cudaGetSymbolAddress(g_noalloc_scratch)", (int)e);
+    }
+    if (dev < 64) cache[dev] = ptr;
+    *out = ptr;
+    return IRBFN_OK;
+}
+
 extern "C" {
 
 int irbfn_abi_version(void) { return IRBFN_ABI_VERSION; }
@@ -316,6 +346,27 @@ static int forward_impl(const float* x, const float* centers, const float* log_s
         if (e != cudaSuccess) return note_cuda_error("split_reduce_kernel", (int)e);
     }
     return IRBFN_OK;
+}
+
+// No counterpart in the reference (include/irbfn_b200.h).
+int irbfn_forward_noalloc(const float* x, const float* centers, const float* log_sigs, const float* W,
+                          const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
+                          float* hidden, int64_t B, int R, int K, int D, int O, int basis,
+                          irbfn_stream_t stream) {
+    const size_t need = (y != nullptr && O > 0) ? irbfn_forward_workspace_bytes(B, R, K, D, O, gd != nullptr) : 0;
+    if (need > (size_t)IRBFN_NOALLOC_SCRATCH_BYTES) {
+        snprintf(g_detail, sizeof(g_detail),
+                 "irbfn_forward_noalloc: this shape needs %zu bytes of scratch, the built-in array holds %u; "
+                 "use irbfn_forward with a caller-owned workspace", need, (unsigned)IRBFN_NOALLOC_SCRATCH_BYTES);
+        return IRBFN_ERR_WORKSPACE;
+    }
+    void* scratch = nullptr;
+    if (need > 0) {
+        const int rc = noalloc_scratch_address(&scratch);
+        if (rc != IRBFN_OK) return rc;
+    }
+    return forward_impl(x, centers, log_sigs, W, bias, gate, gd, y, hidden, nullptr, B, R, K, D, O, basis, scratch,
+                        need > 0 ? (size_t)IRBFN_NOALLOC_SCRATCH_BYTES : 0, stream);
 }
 
 int irbfn_forward_plan(int R, int K, int D, int O, int smem_limit_bytes, int* regions_per_stage,
