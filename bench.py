@@ -419,6 +419,20 @@ def extras(net, params, cfg, dev, world, args):
         gstep_n = GraphedTrainStep(st_n, x.shape[0], GB, loss="l2").load(x, y)
         ms_graph_nccl = timed(lambda: gstep_n(), args.steps, args.warmup)
         del gstep_n, st_n
+    # the same step with gate-sparse parameter gradients (irbfn_backward_sparse, gate_tol = 2^-24): the backward
+    # skips the (sample, region) pairs whose gate cannot move a gradient; the forward stays dense
+    GATE_TOL = 2.0 ** -24
+    st_s = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev, gate_tol=GATE_TOL)
+    st_s.enable_peer_allreduce()
+    ms_t_sp = timed(lambda: train_step(st_s, x, y, GB), args.steps, args.warmup)
+    gstep_s = GraphedTrainStep(st_s, x.shape[0], GB, loss="l2").load(x, y)
+    ms_graph_sp = timed(lambda: gstep_s(), args.steps, args.warmup)
+    st_s.flat.copy_(state.flat)
+    grad_step(st_s, x, y, GB)
+    grad_step(state, x, y, GB)
+    sp_dev = max(float((st_s.gviews[k].double() - state.gviews[k].double()).norm() / state.gviews[k].double().norm())
+                 for k in state.gviews)
+    del gstep_s, st_s
     # where the step's time goes: this rank's kernels alone (no collective: global batch = shard), the
     # NCCL all-reduce of the flat gradient alone, and the rest (launch gaps, rank skew)
     st_l = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev)
@@ -437,7 +451,9 @@ def extras(net, params, cfg, dev, world, args):
                   "allreduce": how, "ms_graph_nccl": ms_graph_nccl,
                   "ms_kernels_this_rank": ms_local, "ms_nccl_allreduce_alone": ms_ar,
                   "ms_fwd_vjp_allreduce": ms_g, "allreduce_bytes": int(state._grad_ext.numel() * 4),
-                  "lane_ops_T_per_s": lane_step * GB / (min(ms_t, ms_graph) * 1e-3) / 1e12}
+                  "lane_ops_T_per_s": lane_step * GB / (min(ms_t, ms_graph) * 1e-3) / 1e12,
+                  "gate_sparse_vjp": {"gate_tol": GATE_TOL, "ms_eager": ms_t_sp, "ms_graph": ms_graph_sp,
+                                      "grad_rel_l2_vs_dense_max_over_leaves": sp_dev}}
 
     # 8(e) result check on hardware: the NCCL-reduced gradient of the sharded step against the gradient of
     # the whole batch on one device (rank 0 holds the full batch too); per-leaf ||g - g1|| / ||g1||
@@ -565,8 +581,21 @@ def train_case(fixture, loss, GB, dev, rank, world, args, timed):
     gstep = GraphedTrainStep(state, x.shape[0], GB, loss=loss).load(x, y)
     ms_graph = timed(lambda: gstep(), steps, 3)
     lane = R * K * (2 * D + 2) + K * O + R * K * (3 * D + 5) + 2 * K * O
+    sparse = None
+    if R > 1:   # gate-sparse parameter gradients (irbfn_backward_sparse), as in c3
+        st_s = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev, gate_tol=2.0 ** -24)
+        st_s.enable_peer_allreduce()
+        gstep_s = GraphedTrainStep(st_s, x.shape[0], GB, loss=loss).load(x, y)
+        ms_graph_sp = timed(lambda: gstep_s(), steps, 3)
+        st_s.flat.copy_(state.flat)
+        grad_step(st_s, x, y, GB, loss)
+        grad_step(state, x, y, GB, loss)
+        dev_sp = max(float((st_s.gviews[k].double() - state.gviews[k].double()).norm() / state.gviews[k].double().norm())
+                     for k in state.gviews)
+        sparse = {"gate_tol": 2.0 ** -24, "ms_graph": ms_graph_sp, "grad_rel_l2_vs_dense_max_over_leaves": dev_sp}
+        del gstep_s, st_s
     return {"shape": "R%d_K%d_D%d_O%d" % (R, K, D, O), "loss": loss, "global_batch": GB, "n_gpus": world,
-            "ms_eager": ms_t, "ms_graph": ms_graph, "ms_fwd_loss_vjp_allreduce": ms_g,
+            "ms_eager": ms_t, "ms_graph": ms_graph, "ms_fwd_loss_vjp_allreduce": ms_g, "gate_sparse_vjp": sparse,
             "lane_ops_T_per_s": lane * GB / (ms_g * 1e-3) / 1e12,
             "allreduce_bytes": int(state._grad_ext.numel() * 4), "allreduce": how}
 
@@ -686,11 +715,16 @@ def other_configs(dev, world, args, timed):
     res["fwd_vjp_C5"] = {"queries_per_gpu": B5b, "ms": ms5b, "queries_per_s": world * B5b / (ms5b * 1e-3),
                          "algorithmic_tflops": (R * K * (3 * D + 2) + R * K * (5 * D + 9) + 6 * K * O) * B5b
                                                / (ms5b * 1e-3) / 1e12, "timed_steps": 2, "warmup": 1}
+    ms5bs = timed(lambda: (ops.forward_sparse(x5[:B5b], c5, ls5, W5, b5, gd=gd5, basis=0, tol_abs=1e-6 * y5scale,
+                                              out=y5[:B5b]),
+                           ops.backward(x5[:B5b], c5, ls5, W5, dy5, gd=gd5, basis=0, grad_mask=ops.GRAD_PARAMS,
+                                        flat_out=flat, gate_tol=2.0 ** -24)), 2, 1)
+    res["fwd_vjp_C5"]["ms_gate_sparse"] = ms5bs
     lane5b = lane5 + R * K * (3 * D + 5) + 2 * K * O
     res["c5_summary"] = {"shape": "R64_K4096_D6_O16", "n_gpus": world, "fwd_ms_per_2p24": ms5,
                          "fwd_gate_sparse_ms_per_2p24": ms5s, "fwd_gate_sparse_skipped_fraction": sk5 / max(1, sk5 + dn5),
                          "fwd_lane_ops_T_per_s": lane5 * B5 / (ms5 * 1e-3) / 1e12,
-                         "fwd_vjp_ms_per_2p22": ms5b, "fwd_vjp_lane_ops_T_per_s": lane5b * B5b / (ms5b * 1e-3) / 1e12}
+                         "fwd_vjp_ms_per_2p22": ms5b, "fwd_vjp_gate_sparse_ms_per_2p22": ms5bs, "fwd_vjp_lane_ops_T_per_s": lane5b * B5b / (ms5b * 1e-3) / 1e12}
     return res
 
 

@@ -32,7 +32,7 @@ DYN_FRENET_MULT, DYN_FRENET_ONESTEP_AUX, DYN_ST_MULT, DYN_ST_ONESTEP_AUX = 0, 1,
 EXPORTED_SYMBOLS = (
     "irbfn_abi_version", "irbfn_error_string", "irbfn_last_error_detail", "irbfn_forward_workspace_bytes", "irbfn_forward",
     "irbfn_forward_gate", "irbfn_forward_noalloc", "irbfn_forward_sparse_workspace_bytes", "irbfn_forward_sparse",
-    "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_region_gate",
+    "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_backward_sparse", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_forward_plan",
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
     "irbfn_gather_rows", "irbfn_lattice_queries", "irbfn_grid_index", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
@@ -95,6 +95,9 @@ def load():
     lib.irbfn_backward.restype = i
     lib.irbfn_backward.argtypes = [p, p, p, p, p, C.POINTER(GateDesc), p, p, p, p, p, p, p, p,
                                    i64, i, i, i, i, i, u, p, sz, p]
+    lib.irbfn_backward_sparse.restype = i
+    lib.irbfn_backward_sparse.argtypes = [p, p, p, p, p, C.POINTER(GateDesc), p, p, p, p, p, p, p, p,
+                                          i64, i, i, i, i, i, u, C.c_float, p, sz, p]
     lib.irbfn_region_gate.restype = i
     lib.irbfn_region_gate.argtypes = [p, C.POINTER(GateDesc), p, i64, i, i, p]
     lib.irbfn_softmax_gate.restype = i

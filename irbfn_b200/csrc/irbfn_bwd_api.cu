@@ -14,6 +14,11 @@ int launch_bwd_p_d5(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream
 int launch_bwd_p_d6(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_p_d7(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_p_d8(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_ps_d4(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);   // gate-sparse (SPARSE = 1); -1: none
+int launch_bwd_ps_d5(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_ps_d6(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_ps_d7(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_ps_d8(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_pw_d4(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_pw_d5(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_pw_d6(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
@@ -301,12 +306,42 @@ size_t irbfn_backward_workspace_bytes(int64_t B, int R, int K, int D, int O, uns
     return a.total > b.total ? a.total : b.total;
 }
 
+// gate_thr < 0: dense.  gate_thr >= 0: parameter-gradient terms of (query, region) pairs with gamma <= gate_thr are
+// dropped where a gate-sparse instantiation exists (irbfn_backward_sparse).
+static int backward_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
+                         const float* gate, const IrbfnGateDesc* gd, const float* dy,
+                         const float* dhidden, float* dcenters, float* dlog_sigs, float* dW, float* dbias,
+                         float* dx, float* dgate, int64_t B, int R, int K, int D, int O, int basis,
+                         unsigned grad_mask, float gate_thr, void* workspace, size_t workspace_bytes,
+                         irbfn_stream_t stream);
+
 int irbfn_backward(const float* x, const float* centers, const float* log_sigs, const float* W,
                    const float* gate, const IrbfnGateDesc* gd, const float* dy,
                    const float* dhidden, float* dcenters, float* dlog_sigs, float* dW, float* dbias,
                    float* dx, float* dgate, int64_t B, int R, int K, int D, int O, int basis,
                    unsigned grad_mask, void* workspace, size_t workspace_bytes,
                    irbfn_stream_t stream) {
+    return backward_impl(x, centers, log_sigs, W, gate, gd, dy, dhidden, dcenters, dlog_sigs, dW, dbias, dx, dgate, B,
+                         R, K, D, O, basis, grad_mask, -1.0f, workspace, workspace_bytes, stream);
+}
+
+int irbfn_backward_sparse(const float* x, const float* centers, const float* log_sigs, const float* W,
+                          const float* gate, const IrbfnGateDesc* gd, const float* dy,
+                          const float* dhidden, float* dcenters, float* dlog_sigs, float* dW, float* dbias,
+                          float* dx, float* dgate, int64_t B, int R, int K, int D, int O, int basis,
+                          unsigned grad_mask, float gate_tol, void* workspace, size_t workspace_bytes,
+                          irbfn_stream_t stream) {
+    if (!(gate_tol >= 0.0f)) return IRBFN_ERR_BAD_DIMS;   // also rejects NaN
+    return backward_impl(x, centers, log_sigs, W, gate, gd, dy, dhidden, dcenters, dlog_sigs, dW, dbias, dx, dgate, B,
+                         R, K, D, O, basis, grad_mask, gate_tol, workspace, workspace_bytes, stream);
+}
+
+static int backward_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
+                         const float* gate, const IrbfnGateDesc* gd, const float* dy,
+                         const float* dhidden, float* dcenters, float* dlog_sigs, float* dW, float* dbias,
+                         float* dx, float* dgate, int64_t B, int R, int K, int D, int O, int basis,
+                         unsigned grad_mask, float gate_thr, void* workspace, size_t workspace_bytes,
+                         irbfn_stream_t stream) {
     if (B < 0 || R <= 0 || K <= 0 || D <= 0 || O < 0) return IRBFN_ERR_BAD_DIMS;
     if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
     if (basis != IRBFN_BASIS_GAUSSIAN && basis != IRBFN_BASIS_INVERSE_QUADRATIC)
@@ -364,7 +399,13 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             // the bias gradient's column sums of dy ride along in the chunk-0 CTAs (one thread per column and
             // row phase); outputs wider than a CTA has threads fall back to the separate pass
             const bool in_kernel_db = (grad_mask & IRBFN_GRAD_KERNEL) && Oeff > 0 && Oeff <= 128;
-            const bool wide = bwdpw_applies(R, Oeff, dhidden != nullptr) && plan_bwd_pw(B, R, K, DT, Oeff, OT, sms, smem, &pw);
+            // gate-sparse calls take the thread-private kernel (it skips per (warp, query); the region-lane kernel
+            // cannot: its lanes ARE the regions) whenever that kernel forms dh in the thread
+            const bool sparse = gate_thr >= 0.0f && R > 1;
+            const bool sparse_p = sparse && plan_bwd_p(B, R, K, DT, D, Oeff, OT, dhidden != nullptr, sms, smem, &pp, 1) &&
+                                  pp.dht && pp.part_floats <= L.max_part_floats;
+            const bool wide = !sparse_p && bwdpw_applies(R, Oeff, dhidden != nullptr) &&
+                              plan_bwd_pw(B, R, K, DT, Oeff, OT, sms, smem, &pw);
             if (wide) {
                 // several regions share a wide readout: lanes = regions, dh from a per-tile table, dW from the
                 // region-summed activation (irbfn_bwd_pw.cuh)
@@ -390,7 +431,7 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
                 pp = BwdPPlan{};
                 pp.splits = pw.splits; pp.PW = pw.PW;
             } else {
-            if (!plan_bwd_p(B, R, K, DT, D, Oeff, OT, dhidden != nullptr, sms, smem, &pp)) return IRBFN_ERR_BAD_DIMS;
+            if (!sparse_p && !plan_bwd_p(B, R, K, DT, D, Oeff, OT, dhidden != nullptr, sms, smem, &pp)) return IRBFN_ERR_BAD_DIMS;
             if (pp.part_floats > L.max_part_floats) return IRBFN_ERR_WORKSPACE;
             if ((long long)R * pp.splits >= (1ll << 31)) return IRBFN_ERR_BAD_DIMS;   // reduce_p_kernel's term index
             BwdPArgs a{};
@@ -402,8 +443,19 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
             a.nchunks = pp.nchunks; a.splits = pp.splits; a.pairs_per_chunk = pp.pairs_per_chunk; a.ppw = pp.ppw;
             a.TQ = pp.TQ; a.Kspan = pp.Kspan; a.Rspan = pp.Rspan;
             a.write_cls = first ? 1 : 0;
+            a.gate_thr = gate_thr;
             const int grid = pp.nchunks * pp.splits;
-            int e;
+            int e = -1;
+            if (sparse) {   // gate-sparse instantiation, where one exists
+                switch (DT) {
+                    case 4: e = launch_bwd_ps_d4(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                    case 5: e = launch_bwd_ps_d5(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                    case 6: e = launch_bwd_ps_d6(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                    case 7: e = launch_bwd_ps_d7(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                    default: e = launch_bwd_ps_d8(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
+                }
+            }
+            if (e < 0)
             switch (DT) {
                 case 4: e = launch_bwd_p_d4(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;
                 case 5: e = launch_bwd_p_d5(a, OT, basis, pp.dht, grid, pp.NT, pp.smem_bytes, st); break;

@@ -49,6 +49,8 @@ struct BwdPArgs {
     int Kspan;              // columns of the dh table (even)
     int Rspan;              // columns of the gate table, + 1 zero column at index Rspan
     int write_cls;          // 1: write dC / dLS partials (first output window only)
+    // ---- read by the SPARSE instantiations only; behind the dense fields so their parameter offsets stay put ----
+    float gate_thr;         // a (query, region) pair with gamma <= gate_thr is dropped (irbfn_backward_sparse)
 };
 
 __device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
@@ -93,8 +95,14 @@ __device__ __forceinline__ void db_flush(const float* dbs, float* part_db, int s
 __host__ __device__ constexpr int bwdp_xs(int D) { return ((D + 3) / 4) * 4; }
 __host__ __device__ inline int bwdp_ds(int O) { return O <= 0 ? 0 : (O <= 2 ? 2 : ((O + 3) / 4) * 4); }
 
-template <int D, int OT, int BASIS, int NKP, int DHT>
+// SPARSE = 1 (gate-sparse parameter gradients, irbfn_backward_sparse; NKP == 1 only): the threads of a warp hold
+// kernel pairs of at most two neighbouring regions and a query is the broadcast operand of the whole CTA, so
+// "this query's gate is <= gate_thr for every region this warp holds" is a WARP-UNIFORM predicate: the warp ballots
+// it for 32 queries at a time and evaluates only the set bits.  No binning or sorting of the queries is needed (unlike the
+// query-stationary forward, irbfn_sparse.cu), and the partial sums keep their fixed order: still deterministic.
+template <int D, int OT, int BASIS, int NKP, int DHT, int SPARSE = 0>
 __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bwd_p_kernel(const BwdPArgs a) {
+    static_assert(SPARSE == 0 || NKP == 1, "the warp-uniform skip test reads the thread's single kernel pair");
     constexpr int OTS = OT > 0 ? OT : 1;
     constexpr int PW = D + 1 + OT;
     constexpr int XS = bwdp_xs(D);
@@ -160,6 +168,20 @@ __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bw
             }
         }
         contig[p] = (kidx[p][1] == kidx[p][0] + 1) && ((kidx[p][0] & 1) == 0);
+    }
+
+    // gate-sparse: the contiguous range of gate-table columns (regions) this warp's pairs belong to; a warp without
+    // pairs gets an empty range and skips every query
+    int wr_lo = Rspan, wr_hi = -1;
+    if (SPARSE) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            if (ridx[0][h] < Rspan) { wr_lo = min(wr_lo, ridx[0][h]); wr_hi = max(wr_hi, ridx[0][h]); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            wr_lo = min(wr_lo, __shfl_xor_sync(0xffffffffu, wr_lo, o));
+            wr_hi = max(wr_hi, __shfl_xor_sync(0xffffffffu, wr_hi, o));
+        }
     }
 
     float2 aC[NKP][D], aL[NKP], aW[NKP][OTS];
@@ -298,6 +320,32 @@ __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bw
             __syncthreads();
         }
 
+        if (SPARSE) {
+            // ---- gate-sparse: 32 queries at a time, lane l looks at query qb + l and asks whether any region this
+            // warp holds pairs of has gamma > gate_thr for it; the warp then walks the set bits of the ballot.  A
+            // skipped query costs nothing beyond its share of the ballot (one LDS + compare per region of the warp).
+            for (int qb = 0; qb < tq; qb += 32) {
+                const int ql = qb + (tid & 31);
+                bool live = false;
+                if (ql < tq) {
+                    const float* gq0 = sb + st_g + (size_t)ql * GS;    // row stride Rspan + 1: odd for the shipped shapes
+                    for (int rr = wr_lo; rr <= wr_hi; ++rr) live |= gq0[rr] > a.gate_thr;
+                }
+                unsigned m = __ballot_sync(0xffffffffu, live);
+                while (m) {
+                    const int b0 = __ffs(m) - 1;
+                    m &= m - 1;
+                    if (m) {
+                        const int b1 = __ffs(m) - 1;
+                        m &= m - 1;
+                        eval(sb, qb + b0);
+                        eval(sb, qb + b1);
+                    } else {
+                        eval(sb, qb + b0);
+                    }
+                }
+            }
+        } else {
         // ---- hot loop over the queries of the tile, two at a time for ILP ----
         int q = 0;
         for (; q + 1 < tq; q += 2) {
@@ -305,6 +353,7 @@ __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bw
             eval(sb, q + 1);
         }
         if (q < tq) eval(sb, q);
+        }
         if (!DHT) __syncthreads();  // the dh table is rebuilt by the next tile
     }
     cp_async_wait_all();
@@ -335,9 +384,9 @@ __global__ void __launch_bounds__((NKP == 1 && OT <= 4) ? 640 : 384, 1) irbfn_bw
 // kernel pairs per thread as a function of the output window: keeps the accumulators in registers
 __host__ __device__ constexpr int bwd_p_nkp_for(int OT) { return OT <= 4 ? IRBFN_BWDP_NKP_NARROW : 1; }
 
-template <int D, int OT, int BASIS, int DHT>
+template <int D, int OT, int BASIS, int DHT, int SPARSE = 0>
 inline int launch_bwd_p_inst(const BwdPArgs& a, int grid, int nt, size_t smem, cudaStream_t st) {
-    auto kern = irbfn_bwd_p_kernel<D, OT, BASIS, bwd_p_nkp_for(OT), DHT>;
+    auto kern = irbfn_bwd_p_kernel<D, OT, BASIS, bwd_p_nkp_for(OT), DHT, SPARSE>;
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     kern<<<grid, nt, smem, st>>>(a);
@@ -365,6 +414,33 @@ inline int launch_bwd_p(const BwdPArgs& a, int OT, int basis, int dht, int grid,
         case 10: return launch_bwd_p_ot<D, 10>(a, basis, dht, grid, nt, smem, st);
         case 16: return launch_bwd_p_ot<D, 16>(a, basis, dht, grid, nt, smem, st);
         default: return (int)cudaErrorInvalidValue;
+    }
+}
+
+// Gate-sparse variants (SPARSE = 1): every output window and both dh forms, one kernel pair per thread.  Returns -1
+// when no sparse instantiation exists (two pairs per thread): the caller launches the dense kernel, which computes
+// the same sums without skipping.
+template <int D, int OT>
+inline int launch_bwd_p_sparse_ot(const BwdPArgs& a, int basis, int dht, int grid, int nt, size_t smem, cudaStream_t st) {
+    constexpr int CAN_DHT = OT > 0 ? 1 : 0;
+    if (basis == IRBFN_BASIS_GAUSSIAN)
+        return (dht && CAN_DHT) ? launch_bwd_p_inst<D, OT, IRBFN_BASIS_GAUSSIAN, CAN_DHT, 1>(a, grid, nt, smem, st)
+                                : launch_bwd_p_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 0, 1>(a, grid, nt, smem, st);
+    return (dht && CAN_DHT) ? launch_bwd_p_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, CAN_DHT, 1>(a, grid, nt, smem, st)
+                            : launch_bwd_p_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 0, 1>(a, grid, nt, smem, st);
+}
+
+template <int D>
+inline int launch_bwd_p_sparse(const BwdPArgs& a, int OT, int basis, int dht, int grid, int nt, size_t smem,
+                               cudaStream_t st) {
+    if (bwd_p_nkp_for(OT) != 1) return -1;
+    switch (OT) {
+        case 2: return launch_bwd_p_sparse_ot<D, 2>(a, basis, dht, grid, nt, smem, st);
+        case 4: return launch_bwd_p_sparse_ot<D, 4>(a, basis, dht, grid, nt, smem, st);
+        case 8: return launch_bwd_p_sparse_ot<D, 8>(a, basis, dht, grid, nt, smem, st);
+        case 10: return launch_bwd_p_sparse_ot<D, 10>(a, basis, dht, grid, nt, smem, st);
+        case 16: return launch_bwd_p_sparse_ot<D, 16>(a, basis, dht, grid, nt, smem, st);
+        default: return -1;
     }
 }
 

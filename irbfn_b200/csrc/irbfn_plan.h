@@ -170,8 +170,11 @@ inline size_t bwdp_smem_floats(int TQ, int D, int O, int Kspan, int Rspan, int h
     return 2 * st + (dht ? 0 : (size_t)TQ * Kspan) + kDbScratch_h;
 }
 
+// sparse = 1 (irbfn_backward_sparse): dh is formed in the thread whenever one output window covers O, also when
+// several regions share the chunk's kernels -- the shared per-tile dh table serves every (query, region) pair, and a
+// gate-sparse call evaluates only a fraction of them.
 inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT, int has_dhid, int sms,
-                       int smem_limit, BwdPPlan* p) {
+                       int smem_limit, BwdPPlan* p, int sparse = 0) {
     const long long RK = (long long)R * K;
     if (RK <= 0 || RK > (1ll << 30)) return false;
     const int P = (int)((RK + 1) / 2);
@@ -203,7 +206,8 @@ inline bool plan_bwd_p(long long B, int R, int K, int D, int Dsrc, int O, int OT
     // one region (a per-tile dh table would be used once, and costs 227 KB-limited tiles of ~80 queries)
     const bool narrow = O >= 1 && O <= 4 && (OT == 2 || OT == 4);
     const bool lone = O >= 1 && O <= 16 && OT >= O && flen < K;
-    const int dht = (!has_dhid && (narrow || lone)) ? 1 : 0;
+    const bool any1 = sparse && O >= 1 && O <= 16 && OT >= O;
+    const int dht = (!has_dhid && (narrow || lone || any1)) ? 1 : 0;
     int TQ = 256;
     while (TQ >= 4 && bwdp_smem_floats(TQ, D, O, Kspan, Rspan, has_dhid, dht) * sizeof(float) > (size_t)smem_limit)
         TQ -= 4;

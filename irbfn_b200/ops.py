@@ -194,11 +194,12 @@ def _workspace(nbytes: int, device) -> Optional[torch.Tensor]:
 
 def backward(x, centers, log_sigs, kernel, dy=None, *, dhidden=None, gate=None,
              gd: GatePack = None, basis: int = BASIS_GAUSSIAN, grad_mask: int = GRAD_PARAMS,
-             flat_out: Optional[torch.Tensor] = None):
+             flat_out: Optional[torch.Tensor] = None, gate_tol: Optional[float] = None):
     """VJP of the forward (irbfn_backward).  Returns a dict with the requested leaves:
     centers, log_sigs, kernel, bias, x, gate.  If ``flat_out`` is given the parameter
     gradients are written into that flat buffer in the order [centers, log_sigs, kernel,
-    bias] (the all-reduce payload) and the dict holds views of it."""
+    bias] (the all-reduce payload) and the dict holds views of it.  ``gate_tol`` (>= 0): gate-sparse parameter
+    gradients (irbfn_backward_sparse) -- terms of (query, region) pairs with gamma <= gate_tol are left out."""
     lib = _lib.load()
     _chk(x, "x")
     B, D = x.shape
@@ -239,13 +240,16 @@ def backward(x, centers, log_sigs, kernel, dy=None, *, dhidden=None, gate=None,
     with torch.cuda.device(dev):
         nbytes = lib.irbfn_backward_workspace_bytes(B, R, K, D, O, grad_mask)
         ws = _workspace(nbytes, dev)
-        rc = lib.irbfn_backward(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(gate),
-                                gd.ref() if gd is not None else None, _ptr(dy), _ptr(dhidden),
-                                _ptr(out.get("centers")), _ptr(out.get("log_sigs")),
-                                _ptr(out.get("kernel")), _ptr(out.get("bias")), _ptr(out.get("x")),
-                                _ptr(out.get("gate")), B, R, K, D, O, basis, grad_mask, _ptr(ws),
-                                nbytes, _stream())
-    _lib.check(rc, "irbfn_backward")
+        head = (_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(gate),
+                gd.ref() if gd is not None else None, _ptr(dy), _ptr(dhidden),
+                _ptr(out.get("centers")), _ptr(out.get("log_sigs")),
+                _ptr(out.get("kernel")), _ptr(out.get("bias")), _ptr(out.get("x")),
+                _ptr(out.get("gate")), B, R, K, D, O, basis, grad_mask)
+        if gate_tol is None:
+            rc = lib.irbfn_backward(*head, _ptr(ws), nbytes, _stream())
+        else:
+            rc = lib.irbfn_backward_sparse(*head, float(gate_tol), _ptr(ws), nbytes, _stream())
+    _lib.check(rc, "irbfn_backward" if gate_tol is None else "irbfn_backward_sparse")
     return out
 
 

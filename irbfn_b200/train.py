@@ -29,7 +29,8 @@ class TrainState:
     """step / params / opt_state holder (the reference's flax TrainState, scripts/train_nmpc.py:236)."""
 
     def __init__(self, module: WCRBFNet, params: dict, lr: float, max_grad_norm: float = 1.0,
-                 b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, device=None):
+                 b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, device=None,
+                 gate_tol: Optional[float] = None):
         if not isinstance(module, WCRBFNet):
             raise TypeError("TrainState drives WCRBFNet (the shape train_nmpc*.py trains)")
         p = _unwrap(params)
@@ -80,6 +81,9 @@ class TrainState:
         self.peer = None
         self.peer_status = None
         self.gate_buf = None          # (B,R) gate written by the forward, read by the backward
+        # None: dense parameter gradients.  >= 0: gate-sparse (irbfn_backward_sparse): the terms of (sample, region)
+        # pairs whose gate is <= gate_tol are left out of the parameter gradients (2^-24 changes them by ~4e-8)
+        self.gate_tol = gate_tol
         self.fused_tail = n + 1 <= ops.fused_update_max_n() if device.type == "cuda" else False
 
     def enable_peer_allreduce(self) -> str:
@@ -252,7 +256,7 @@ def _local_grad(state: TrainState, x: torch.Tensor, y: torch.Tensor, gb: int, lo
         lval = lv[0]
     n = state.grad.numel()
     ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gate=state.gate_buf, basis=m._basis,
-                 grad_mask=state.mask, flat_out=state._grad_src[:n])
+                 grad_mask=state.mask, flat_out=state._grad_src[:n], gate_tol=state.gate_tol)
     state._grad_src[n:n + 1].copy_(lval.reshape(1))      # the loss rides along: still one collective, no concat
     return lval
 

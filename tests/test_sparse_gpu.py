@@ -94,3 +94,85 @@ def test_sparse_forward_errors(cuda_device):
         ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=0, tol_abs=-1.0)
     with pytest.raises(IrbfnError):
         ops.forward_sparse(*args, gd=_gd(cfg, dev), basis=7, tol_abs=0.0)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Gate-sparse parameter gradients (irbfn_backward_sparse): the terms of (query, region) pairs with gamma <= gate_tol are
+# left out.  Checked against the reference-executed gradients of the shipped checkpoints and against the DENSE float64
+# oracle at the gradient tolerance every backward test uses (rel-L2 <= 1e-4 per leaf).
+# ---------------------------------------------------------------------------------------------------
+GRAD_TOL = 1e-4
+GATE_TOL = 2.0 ** -24
+LEAVES = (("centers", "g/rbf_list/centers"), ("log_sigs", "g/rbf_list/log_sigs"), ("kernel", "g/linear/kernel"),
+          ("bias", "g/linear/bias"))
+
+
+def _rel_l2(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+@pytest.mark.parametrize("path", WCRBF, ids=[os.path.basename(p)[:-4] for p in WCRBF])
+def test_sparse_backward_matches_reference_gradients_on_shipped_checkpoints(path, cuda_device):
+    ops = _ops()
+    cfg, params, arr = load_golden(path)
+    rb, lin = params["rbf_list"], params["linear"]
+    dev = cuda_device
+    y64 = arr["y64"]
+    args = (_t(arr["x"], dev), _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(lin["kernel"], dev),
+            _t(2 * y64 / y64.size, dev))
+    kw = dict(gd=_gd(cfg, dev), basis=orc.BASIS_IDS[cfg["basis_func"]], grad_mask=ops.GRAD_PARAMS | ops.GRAD_X)
+    g = ops.backward(*args, gate_tol=GATE_TOL, **kw)
+    for leaf, key in LEAVES:
+        assert _rel_l2(g[leaf].cpu().numpy(), arr[key]) < GRAD_TOL, leaf
+    assert _rel_l2(g["x"].cpu().numpy(), arr["g/x"]) < GRAD_TOL          # dx is not affected by gate_tol
+    # deterministic: same fixed partition and order as the dense kernel
+    g2 = ops.backward(*args, gate_tol=GATE_TOL, **kw)
+    for leaf, _ in LEAVES:
+        assert torch.equal(g[leaf], g2[leaf]), leaf
+    # gate_tol = 0 leaves out only terms whose gate is exactly 0
+    g0 = ops.backward(*args, gate_tol=0.0, **kw)
+    for leaf, key in LEAVES:
+        assert _rel_l2(g0[leaf].cpu().numpy(), arr[key]) < GRAD_TOL, leaf
+
+
+@pytest.mark.parametrize("shape", [(1023, 3, 7, 4, 2), (5000, 12, 100, 8, 2), (3000, 27, 30, 8, 10), (2049, 64, 40, 6, 16),
+                                   (777, 5, 33, 5, 4), (4000, 130, 6, 7, 18)],
+                         ids=lambda s: "B%d_R%d_K%d_D%d_O%d" % s)
+def test_sparse_backward_matches_dense_oracle_with_sharp_gates(shape, cuda_device):
+    """Uniform queries, sharp gates (most (query, region) pairs are skipped), narrow and wide outputs, odd K."""
+    ops = _ops()
+    B, R, K, D, O = shape
+    cfg, p, x = _synthetic(43, B, R, K, D, O, S=min(3, D), nb=(4, 3, 2))
+    cfg["delta"] = [40.0] * len(cfg["delta"])
+    dev = cuda_device
+    rng = np.random.default_rng(5)
+    dy = (rng.standard_normal((B, O)) / B).astype(np.float32)
+    x64 = x.astype(np.float64)
+    gamma = orc.region_activation(x64, cfg["num_regions"], cfg["lower_bounds"], cfg["upper_bounds"], cfg["delta"],
+                                  cfg["dimension_ranges"])
+    assert (gamma <= GATE_TOL).mean() > 0.3            # the case really is sparse
+    for basis in (0, 1):
+        ref = orc.backward(x64, p["centers"], p["log_sigs"], p["kernel"], p["bias"], gamma, dy.astype(np.float64), basis)
+        args = (_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev), _t(dy, dev))
+        g = ops.backward(*args, gd=_gd(cfg, dev), basis=basis, gate_tol=GATE_TOL)
+        for leaf in ("centers", "log_sigs", "kernel", "bias"):
+            assert _rel_l2(g[leaf].cpu().numpy(), ref[leaf]) < GRAD_TOL, (basis, leaf)
+        # an externally supplied gate (what a training step hands over from irbfn_forward_gate) takes the same path
+        gate = ops.region_gate(_t(x, dev), _gd(cfg, dev), R)
+        ge = ops.backward(*args, gate=gate, basis=basis, gate_tol=GATE_TOL)
+        for leaf in ("centers", "log_sigs", "kernel", "bias"):
+            assert torch.equal(g[leaf], ge[leaf]), (basis, leaf)
+
+
+def test_sparse_backward_errors(cuda_device):
+    from irbfn_b200._lib import IrbfnError
+    ops = _ops()
+    cfg, p, x = _synthetic(3, 64, 2, 5, 4, 2)
+    dev = cuda_device
+    args = (_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev),
+            torch.zeros((64, 2), device=dev))
+    with pytest.raises(IrbfnError):
+        ops.backward(*args, gd=_gd(cfg, dev), basis=0, gate_tol=-1.0)
+    with pytest.raises(IrbfnError):
+        ops.backward(*args, gd=_gd(cfg, dev), basis=0, gate_tol=float("nan"))
