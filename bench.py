@@ -252,6 +252,11 @@ def main():
     ms_e2e = timed(lambda i: net.apply_host(params, xh, out=yh), args.steps, args.warmup)
     e2e = {"value": world * B / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
            "h2d_bytes_per_step": int(xh.numel() * 4), "d2h_bytes_per_step": int(yh.numel() * 4)}
+    # opt-in variant: ONE persistent launch whose query tiles wait for their piece of the upload and which stores y
+    # straight into the pinned host buffer (irbfn_forward_streamed); which of the two wins depends on the box's link
+    if ops.upload_streamed_available():
+        e2e["ms_per_step_streamed_single_launch"] = timed(lambda i: net.apply_host(params, xh, out=yh, streamed=True),
+                                                          args.steps, args.warmup)
     # the same sweep through the lattice entry point: the queries are generated on the device from the axis
     # values (a few hundred bytes up), the outputs still come down to pinned host memory every step.  Reported
     # beside the generic host-buffer number, which stays the e2e headline.

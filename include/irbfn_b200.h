@@ -136,6 +136,40 @@ int irbfn_forward_gate(const float* x, const float* centers, const float* log_si
                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
 
 /*
+ * Forward over rows that are still being uploaded (the host-buffer path, bench.py's e2e): irbfn_forward launched
+ * BEFORE its input has arrived.  The caller uploads x in pieces of queries_per_flag rows on other streams and, behind
+ * each piece on the piece's stream, stores a non-zero word into the piece's flag (cuStreamWriteValue32 or a 4-byte
+ * copy; irbfn_upload_streamed does both steps).  The persistent kernel hands its 1,024-query tiles out through a
+ * counter and waits for the flag of a tile's piece before it touches the tile's rows, so the upload of later pieces
+ * overlaps the evaluation of earlier ones inside ONE launch -- no per-chunk launches, ramps or tails.  y may be device
+ * memory or pinned, device-mapped host memory (the kernel's stores then go straight over PCIe, as full 16-byte
+ * vectors: no download pass).  Replaces the reference's implicit jax.device_put of the whole batch before wcrbf.apply
+ * (irbfn_vs_explicit_frenet.ipynb, cells 8-13).
+ *   ready    device uint32: ceil(B / queries_per_flag) flags followed by ONE tile-counter word; ALL ZERO when this call
+ *            is enqueued (and not written by a copy stream before that)
+ *   queries_per_flag   a multiple of 1,024
+ *   status   optional device int, set to 1 if a piece did not arrive within ~3 s (the result is then undefined)
+ *   O <= 16.  An external gate must be complete in device memory before the call (only x is streamed).
+ */
+int irbfn_forward_streamed(const float* x, const float* centers, const float* log_sigs, const float* W,
+                           const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y, int64_t B,
+                           int R, int K, int D, int O, int basis, uint32_t* ready, int64_t queries_per_flag,
+                           int* status, irbfn_stream_t stream);
+
+/*
+ * The upload side of irbfn_forward_streamed, for a caller that has no copy loop of its own: enqueues the
+ * host->device copies of x (B,D) from PINNED host memory in pieces of queries_per_flag rows, alternating over
+ * num_streams copy streams (one stream's per-copy set-up hides behind another's transfer), each piece followed on its
+ * stream by a cuStreamWriteValue32 that sets the piece's flag.  None of the copy streams may be the stream
+ * irbfn_forward_streamed runs on, and all must be ordered behind the clearing of ready[] (an event).
+ */
+int irbfn_upload_streamed(const float* x_host, float* x_dev, int64_t B, int D, uint32_t* ready,
+                          int64_t queries_per_flag, const irbfn_stream_t* copy_streams, int num_streams);
+/* 1 when the driver offers cuStreamWriteValue32 (irbfn_upload_streamed can run), else 0: ask BEFORE launching
+ * irbfn_forward_streamed, whose tiles would otherwise wait for flags that never come. */
+int irbfn_upload_streamed_available(void);
+
+/*
  * irbfn_forward for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  *

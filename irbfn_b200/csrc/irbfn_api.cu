@@ -223,7 +223,8 @@ size_t irbfn_forward_workspace_bytes(int64_t B, int R, int K, int D, int O, int 
 static int forward_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
                         const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
                         float* hidden, float* gate_out, int64_t B, int R, int K, int D, int O, int basis,
-                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
+                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream,
+                        unsigned* ready = nullptr, int tiles_per_flag = 0, int* stream_status = nullptr);
 
 int irbfn_forward(const float* x, const float* centers, const float* log_sigs, const float* W,
                   const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
@@ -245,7 +246,8 @@ int irbfn_forward_gate(const float* x, const float* centers, const float* log_si
 static int forward_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
                         const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
                         float* hidden, float* gate_out, int64_t B, int R, int K, int D, int O, int basis,
-                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream) {
+                        void* workspace, size_t workspace_bytes, irbfn_stream_t stream,
+                        unsigned* ready, int tiles_per_flag, int* stream_status) {
     if (B < 0 || R <= 0 || K <= 0 || D <= 0) return IRBFN_ERR_BAD_DIMS;
     if (y != nullptr && O <= 0) return IRBFN_ERR_BAD_DIMS;
     if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
@@ -273,7 +275,7 @@ static int forward_impl(const float* x, const float* centers, const float* log_s
     // region over gridDim.y, partial readouts into the workspace, fixed-order reduction afterwards.
     // Without (enough) workspace the unsplit path runs -- same result, more latency.
     int k_per_split = ((K + kFwdKT - 1) / kFwdKT) * kFwdKT;
-    int nsplit = fwd_split(B, R, K, dev.sms, &k_per_split);
+    int nsplit = ready != nullptr ? 1 : fwd_split(B, R, K, dev.sms, &k_per_split);   // streamed input: whole tiles per CTA
     float* part = nullptr;
     if (nsplit > 1 && y != nullptr) {
         if (workspace != nullptr && workspace_bytes >= (size_t)nsplit * (size_t)B * (size_t)O * sizeof(float))
@@ -303,6 +305,11 @@ static int forward_impl(const float* x, const float* centers, const float* log_s
         a.y = ocur > 0 ? (part ? part : y) : nullptr;
         a.hidden = first ? hidden : nullptr;
         a.gate_out = first ? gate_out : nullptr;
+        a.ready = ready;
+        a.tiles_per_flag = tiles_per_flag;
+        a.stream_status = stream_status;
+        if (ready != nullptr)   // the tile counter sits behind the flags
+            a.work_counter = ready + ((B + kFwdTQ - 1) / kFwdTQ + tiles_per_flag - 1) / tiles_per_flag;
         a.B = B;
         a.R = R;
         a.K = K;
@@ -318,7 +325,7 @@ static int forward_impl(const float* x, const float* centers, const float* log_s
         a.num_tiles = (int)tiles;
         const int grid = (int)(tiles < dev.sms ? tiles : dev.sms);
         int e;
-        if (a.gate_out != nullptr) {   // training forward: the variant that also writes the gate
+        if (a.gate_out != nullptr || a.ready != nullptr) {   // the variants that also write the gate / wait for streamed rows
             switch (DT) {
                 case 4: e = launch_fwdm_d4(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
                 case 5: e = launch_fwdm_d5(a, OT, basis, plan.NT, grid, plan.smem_bytes, st); break;
@@ -344,6 +351,65 @@ static int forward_impl(const float* x, const float* centers, const float* log_s
         split_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(part, y, nsplit, n);
         const cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return note_cuda_error("split_reduce_kernel", (int)e);
+    }
+    return IRBFN_OK;
+}
+
+int irbfn_forward_streamed(const float* x, const float* centers, const float* log_sigs, const float* W,
+                           const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y, int64_t B,
+                           int R, int K, int D, int O, int basis, uint32_t* ready, int64_t queries_per_flag,
+                           int* status, irbfn_stream_t stream) {
+    if (ready == nullptr || y == nullptr) return IRBFN_ERR_NULL_POINTER;
+    if (queries_per_flag <= 0 || queries_per_flag % kFwdTQ != 0 || queries_per_flag / kFwdTQ > (1 << 30))
+        return IRBFN_ERR_BAD_DIMS;
+    if (O <= 0 || O > 16) return IRBFN_ERR_BAD_DIMS;   // one output window: a second pass would not wait again
+    if ((B + kFwdTQ - 1) / kFwdTQ >= (1ll << 31)) return IRBFN_ERR_BAD_DIMS;
+    return forward_impl(x, centers, log_sigs, W, bias, gate, gd, y, nullptr, nullptr, B, R, K, D, O, basis, nullptr, 0,
+                        stream, ready, (int)(queries_per_flag / kFwdTQ), status);
+}
+
+// cuStreamWriteValue32 through the runtime's driver entry point (no link against libcuda): a 32-bit store executed
+// by the stream's front end in stream order -- no copy engine, no SM.
+typedef int (*StreamWrite32Fn)(cudaStream_t, unsigned long long, unsigned int, unsigned int);
+static StreamWrite32Fn stream_write32_fn() {
+    static StreamWrite32Fn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            p = nullptr;
+        }
+        return (StreamWrite32Fn)p;
+    }();
+    return fn;
+}
+
+int irbfn_upload_streamed_available(void) { return stream_write32_fn() != nullptr ? 1 : 0; }
+
+int irbfn_upload_streamed(const float* x_host, float* x_dev, int64_t B, int D, uint32_t* ready,
+                          int64_t queries_per_flag, const irbfn_stream_t* copy_streams, int num_streams) {
+    if (!x_host || !x_dev || !ready || !copy_streams) return IRBFN_ERR_NULL_POINTER;
+    if (B < 0 || D <= 0 || queries_per_flag <= 0 || queries_per_flag % kFwdTQ != 0 || num_streams <= 0)
+        return IRBFN_ERR_BAD_DIMS;
+    StreamWrite32Fn write32 = stream_write32_fn();
+    if (write32 == nullptr) {
+        snprintf(g_detail, sizeof(g_detail), "irbfn_upload_streamed: the driver has no cuStreamWriteValue32");
+        return IRBFN_ERR_LAUNCH;
+    }
+    int64_t p = 0;
+    for (int64_t lo = 0; lo < B; lo += queries_per_flag, ++p) {
+        const int64_t hi = lo + queries_per_flag < B ? lo + queries_per_flag : B;
+        cudaStream_t st = (cudaStream_t)copy_streams[p % num_streams];   // pieces alternate over the copy streams: one
+                                                                         // stream's per-copy set-up hides behind another's transfer
+        const cudaError_t e = cudaMemcpyAsync(x_dev + lo * D, x_host + lo * D, (size_t)(hi - lo) * D * sizeof(float),
+                                              cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) return note_cuda_error("cudaMemcpyAsync (streamed upload)", (int)e);
+        const int r = write32(st, (unsigned long long)(uintptr_t)(ready + p), 1u, 0u);
+        if (r != 0) {
+            snprintf(g_detail, sizeof(g_detail), "cuStreamWriteValue32: CUresult %d", r);
+            return IRBFN_ERR_LAUNCH;
+        }
     }
     return IRBFN_OK;
 }

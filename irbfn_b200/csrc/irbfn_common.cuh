@@ -291,6 +291,12 @@ struct FwdArgs {
     unsigned long long* skip_count;   // optional: number of (warp, kernel-chunk, region) evaluations skipped / done
     unsigned* work_counter; // SPARSE with resident parameters: warps fetch their next 128-query unit here (zeroed
                             // by the caller): tiles differ 2-3x in active regions, a static split leaves a long tail
+    // streamed input (STREAM instantiation only, irbfn_forward_streamed): the rows of x arrive WHILE the kernel runs;
+    // ready[p] != 0 once upload piece p (tiles_per_flag tiles of 1,024 queries) has landed -- written behind the
+    // piece's data on its copy stream; work_counter (the word behind the flags) hands the tiles out.
+    const unsigned* ready;
+    int tiles_per_flag;
+    int* stream_status;     // set to 1 if a flag did not arrive within the spin budget (the result is then undefined)
 };
 
 // log-sigma -> the per-kernel scale used in the hot loop.

@@ -37,12 +37,14 @@ namespace irbfn {
 // MODE 0: the plain dense forward.  MODE 1: gate-sparse (perm, masks, compact staging).  MODE 2: dense + the gate
 // written out for a training step's backward.  Separate instantiations: the extra code of modes 1 / 2, even when
 // skipped at run time, changed the register allocation of the wide-output dense variants (C5 forward 2.06 -> 2.33 s).
-constexpr int kFwdDense = 0, kFwdSparse = 1, kFwdGateOut = 2;
+// MODE 3: dense, input rows streamed in while the kernel runs (irbfn_forward_streamed): a tile waits for its flag.
+constexpr int kFwdDense = 0, kFwdSparse = 1, kFwdGateOut = 2, kFwdStream = 3;
 
 template <int D, int OT, int BASIS, int NT, int MODE = kFwdDense>
 __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) {
     constexpr bool SPARSE = MODE == kFwdSparse;
     constexpr bool GOUT = MODE == kFwdGateOut;
+    constexpr bool STREAM = MODE == kFwdStream;
     constexpr int Q = FwdShape::Q, TQ = NT * Q, KT = FwdShape::KT;
     constexpr int OP = OT / 2;            // packed output pairs
     constexpr int OTS = OT > 0 ? OT : 1;
@@ -59,6 +61,7 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
     __shared__ unsigned long long s_cmask[3];   // union over the CTA's warps; three buffers in rotation so that
                                                 // re-zeroing one never races with a later chunk's atomicOr
     __shared__ int s_slot2r[64];                // compact stage slot -> region of the chunk
+    __shared__ unsigned s_tile;                 // STREAM: the tile this CTA fetched from the counter
     float gthr = 0.f;
     unsigned long long n_skip = 0, n_done = 0;
     int parity = 0;
@@ -97,6 +100,35 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
                 if (u >= num_units) break;
             }
             q0 = u * (32 * Q) + (long long)(tid & 31) * Q;      // beyond B on the first round: an empty unit
+        } else if (STREAM) {
+            // Streamed input: the rows of a tile are uploaded WHILE earlier tiles compute.  Tiles are handed out by a
+            // counter (CTAs whose first rows arrived early take more tiles than those that had to wait), and a CTA
+            // waits for the flag of the tile's upload piece -- written behind the piece's data, in stream order --
+            // before it touches the rows.  The rows are then read with COHERENT loads (ld.global.cg): ld.global.nc marks data as constant for
+            // the kernel's lifetime and ptxas hoists such loads above the barrier that follows the wait.
+            __syncthreads();                                   // everyone has consumed s_tile of the previous round
+            if (tid == 0) {
+                const unsigned t = atomicAdd(a.work_counter, 1u);
+                if (t < (unsigned)a.num_tiles) {
+                    const long long t0 = clock64();
+                    unsigned v;
+                    const unsigned* f = a.ready + t / (unsigned)a.tiles_per_flag;   // the flag of the tile's upload piece
+                    for (;;) {
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                        if (v != 0u) break;
+                        if (clock64() - t0 > 6000000000ll) {           // ~3 s: the upload never came
+                            if (a.stream_status != nullptr) atomicExch(a.stream_status, 1);
+                            break;
+                        }
+                        __nanosleep(128);
+                    }
+                }
+                s_tile = t;
+            }
+            __syncthreads();
+            tile = s_tile;
+            if (tile >= a.num_tiles) break;
+            q0 = tile * TQ + (long long)tid * Q;
         } else {
             if (tile >= a.num_tiles) break;
             q0 = tile * TQ + (long long)tid * Q;
@@ -114,6 +146,16 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
                 for (int j = 0; j < D; ++j) {
                     x2[p][j].x = (qi[2 * p] >= 0 && j < a.Dsrc) ? __ldg(a.x + qi[2 * p] * a.Dsrc + j) : 0.f;
                     x2[p][j].y = (qi[2 * p + 1] >= 0 && j < a.Dsrc) ? __ldg(a.x + qi[2 * p + 1] * a.Dsrc + j) : 0.f;
+                }
+            }
+        } else if (STREAM) {
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                const long long qa = q0 + 2 * p, qb = qa + 1;
+#pragma unroll
+                for (int j = 0; j < D; ++j) {
+                    x2[p][j].x = (qa < a.B && j < a.Dsrc) ? __ldcg(a.x + qa * a.Dsrc + j) : 0.f;
+                    x2[p][j].y = (qb < a.B && j < a.Dsrc) ? __ldcg(a.x + qb * a.Dsrc + j) : 0.f;
                 }
             }
         } else {
@@ -151,6 +193,16 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
             } else if (SPARSE) {
                 gate_columns_rows(a.gd, a.x, qi, a.Dsrc, r0, rc, gcol, NT);
             } else {
+                if (STREAM) {
+                    gate_columns_impl(a.gd, [&](int j) {
+                        float4 v;
+                        v.x = q0 + 0 < a.B ? __ldcg(a.x + (q0 + 0) * a.Dsrc + j) : 0.f;
+                        v.y = q0 + 1 < a.B ? __ldcg(a.x + (q0 + 1) * a.Dsrc + j) : 0.f;
+                        v.z = q0 + 2 < a.B ? __ldcg(a.x + (q0 + 2) * a.Dsrc + j) : 0.f;
+                        v.w = q0 + 3 < a.B ? __ldcg(a.x + (q0 + 3) * a.Dsrc + j) : 0.f;
+                        return v;
+                    }, r0, rc, gcol, NT);
+                } else
                 gate_columns(a.gd, a.x, q0, a.B, a.Dsrc, r0, rc, gcol, NT);
             }
             // ---- SPARSE: which regions of the chunk matter to this warp / to the CTA ----
@@ -412,6 +464,19 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
         }
 
         // ---- store y ----
+        // STREAM: y may be pinned host memory.  A thread's four rows are 4 * O consecutive floats, 16-byte aligned when
+        // the launch covers whole rows: written as float4s, so that every PCIe write carries full 32-byte sectors
+        // (scalar 4-byte stores to host memory cost the kernel +600 us per 2^20 queries at O = 2).
+        if (STREAM && OT > 0 && a.ocur == OT && a.ldw == OT && a.o0 == 0 && q0 + Q - 1 < a.B) {
+            float4* yp4 = reinterpret_cast<float4*>(ybase + q0 * OT);
+            float v[Q * OTS];
+#pragma unroll
+            for (int q = 0; q < Q; ++q)
+#pragma unroll
+                for (int op = 0; op < OP; ++op) { v[q * OT + 2 * op] = y2[q][op].x; v[q * OT + 2 * op + 1] = y2[q][op].y; }
+#pragma unroll
+            for (int i = 0; i < OT; ++i) yp4[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        } else
         if (OT > 0) {
 #pragma unroll
             for (int q = 0; q < Q; ++q) {
@@ -450,6 +515,11 @@ inline int launch_fwdm_ot(const FwdArgs& a, int basis, int nt, int grid, size_t 
         if (OT == 0) return (int)cudaErrorInvalidValue;
         if (basis == IRBFN_BASIS_GAUSSIAN) return launch_fwdm_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 256, kFwdSparse>(a, grid, smem, st);
         return launch_fwdm_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 256, kFwdSparse>(a, grid, smem, st);
+    }
+    if (a.ready != nullptr) {                           // streamed input
+        if (OT == 0) return (int)cudaErrorInvalidValue;
+        if (basis == IRBFN_BASIS_GAUSSIAN) return launch_fwdm_inst<D, OT, IRBFN_BASIS_GAUSSIAN, 256, kFwdStream>(a, grid, smem, st);
+        return launch_fwdm_inst<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, 256, kFwdStream>(a, grid, smem, st);
     }
     if (a.gate_out != nullptr) {                        // training forward: also writes the gate
         if (OT == 0) return (int)cudaErrorInvalidValue;

@@ -9,6 +9,8 @@ from __future__ import annotations
 import numpy as np
 import torch
 
+from . import ops
+
 
 class HostPipeline:
     NBUF = 3
@@ -136,3 +138,76 @@ class HostPipeline:
                 out[lo:hi].copy_(self.yd[b][:m], non_blocking=True)
                 self.ev_out[b].record(self.s_out)
         cur.wait_stream(self.s_out)
+
+
+class StreamedPipeline:
+    """Host buffers in, host buffers out, ONE kernel launch (ops.forward_streamed).
+
+    The persistent forward is launched first; the batch is then uploaded in pieces alternating over a few copy streams
+    (one stream's per-copy set-up hides behind another's transfer), each piece followed on its stream by a stream-ordered
+    store that sets the piece's flag; every query tile of the kernel waits for its piece's flag before it reads its
+    rows.  Outputs are stored by the kernel straight into the pinned host buffer.  Compared with HostPipeline (one
+    launch per chunk, a download pass) there is no per-chunk launch ramp / tail and no D2H stage.
+    """
+
+    def __init__(self, device, in_features: int, out_features: int, chunk: int = 1 << 15, copy_streams: int = 3):
+        self.device = torch.device(device)
+        self.D, self.O = in_features, out_features
+        self.chunk = max(1024, (int(chunk) // 1024) * 1024)        # rows per upload piece / flag
+        self.s_ins = [torch.cuda.Stream(self.device) for _ in range(max(1, int(copy_streams)))]
+        self.ev_zero = torch.cuda.Event()
+        self.ev_done = torch.cuda.Event()
+        self.xd = None
+        self.flags = None
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._pin_in = None
+        self._pin_out = None
+
+    def _pinned_in(self, x):
+        if isinstance(x, torch.Tensor) and x.is_pinned() and x.dtype == torch.float32 and x.is_contiguous():
+            return x
+        t = torch.as_tensor(np.ascontiguousarray(np.asarray(x), dtype=np.float32)) if not isinstance(x, torch.Tensor) \
+            else x.float().contiguous()
+        self.ev_done.synchronize()                  # an earlier call may still be uploading from the staging buffer
+        if self._pin_in is None or self._pin_in.shape[0] < t.shape[0]:
+            self._pin_in = torch.empty((t.shape[0], self.D), dtype=torch.float32).pin_memory()
+        buf = self._pin_in[: t.shape[0]]
+        buf.copy_(t)
+        return buf
+
+    def run(self, x, out, launch):
+        """launch(x_dev, y_host, ready, queries_per_flag, status) enqueues ops.forward_streamed on the current stream."""
+        xin = self._pinned_in(x)
+        B = xin.shape[0]
+        if xin.dim() != 2 or xin.shape[1] != self.D:
+            raise ValueError("x must be (B, %d)" % self.D)
+        ret_numpy = out is None
+        if out is None:
+            if self._pin_out is None or self._pin_out.shape[0] < B:
+                self._pin_out = torch.empty((B, self.O), dtype=torch.float32).pin_memory()
+            out = self._pin_out[:B]
+        elif not (isinstance(out, torch.Tensor) and out.is_pinned() and tuple(out.shape) == (B, self.O)):
+            raise ValueError("out must be a pinned CPU tensor of shape (B, %d)" % self.O)
+        if B == 0:
+            return out.numpy().copy() if ret_numpy else out
+        n = (B + self.chunk - 1) // self.chunk
+        if self.xd is None or self.xd.shape[0] < B:
+            self.xd = torch.empty((B, self.D), device=self.device)
+        if self.flags is None or self.flags.numel() < n + 1:
+            self.flags = torch.zeros(n + 1, dtype=torch.int32, device=self.device)
+        cur = torch.cuda.current_stream(self.device)
+        # the previous call's kernel has consumed its uploads (stream order), so flags and tile counter may be cleared;
+        # no copy stream may set a flag before the clear
+        self.flags[:n + 1].zero_()
+        self.ev_zero.record(cur)
+        launch(self.xd[:B], out, self.flags[:n + 1], self.chunk, self.status)
+        for s in self.s_ins:
+            s.wait_event(self.ev_zero)
+        ops.upload_streamed(xin, self.xd[:B], self.flags[:n + 1], self.chunk, self.s_ins)
+        self.ev_done.record(cur)                    # kernel finished => every upload finished and every y row stored
+        if ret_numpy:
+            cur.synchronize()
+            if int(self.status.item()) != 0:
+                raise RuntimeError("irbfn_forward_streamed: an upload piece never arrived")
+            return out.numpy().copy()
+        return out

@@ -178,6 +178,61 @@ def forward_sparse(x, centers, log_sigs, kernel, bias, *, gd: GatePack, basis: i
     return y
 
 
+def forward_streamed(x, centers, log_sigs, kernel, bias, y, ready, queries_per_flag: int, *, gd: GatePack = None,
+                     gate=None, basis: int = BASIS_GAUSSIAN, status=None):
+    """Forward over rows that are still being uploaded (irbfn_forward_streamed).  ``x`` (B,D) is the DEVICE buffer the
+    caller's copy streams are filling piece by piece; ``ready`` a zeroed int32/uint32 CUDA tensor with one flag per
+    piece of ``queries_per_flag`` rows (a multiple of 1,024) plus ONE more word (the kernel's tile counter); a flag is
+    set behind its piece's upload (``upload_streamed``).  ``y`` (B,O): a CUDA tensor or a PINNED CPU tensor (the kernel
+    then stores straight into host memory)."""
+    lib = _lib.load()
+    _chk(x, "x")
+    B, D = x.shape
+    _chk(centers, "centers")
+    R, K, _ = centers.shape
+    _chk(log_sigs, "log_sigs", (R, K))
+    O = kernel.shape[1]
+    _chk(kernel, "kernel", (K, O))
+    _chk(bias, "bias", (O,))
+    if not (isinstance(y, torch.Tensor) and y.dtype == torch.float32 and y.is_contiguous() and tuple(y.shape) == (B, O)
+            and (y.is_cuda or y.is_pinned())):
+        raise ValueError("y must be a contiguous float32 (B,O) CUDA tensor or pinned CPU tensor")
+    if not (ready.is_cuda and ready.dtype in (torch.int32, torch.uint32) and ready.is_contiguous()):
+        raise ValueError("ready must be a contiguous 32-bit integer CUDA tensor")
+    if (ready.numel() - 1) * int(queries_per_flag) < B:
+        raise ValueError("ready has %d flags of %d rows (+ the counter word): fewer than B = %d"
+                         % (ready.numel() - 1, queries_per_flag, B))
+    if B == 0:
+        return y
+    with torch.cuda.device(x.device):
+        rc = lib.irbfn_forward_streamed(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias), _ptr(gate),
+                                        gd.ref() if gd is not None else None, C.c_void_p(y.data_ptr()), B, R, K, D, O,
+                                        basis, _ptr(ready), int(queries_per_flag), _ptr(status), _stream())
+    _lib.check(rc, "irbfn_forward_streamed")
+    return y
+
+
+def upload_streamed_available() -> bool:
+    """Whether the driver offers the stream-ordered 32-bit store ``upload_streamed`` sets its flags with."""
+    return bool(_lib.load().irbfn_upload_streamed_available())
+
+
+def upload_streamed(x_host, x_dev, ready, queries_per_flag: int, copy_streams):
+    """The upload side of ``forward_streamed`` (irbfn_upload_streamed): pinned ``x_host`` (B,D) -> ``x_dev`` in pieces
+    of ``queries_per_flag`` rows alternating over ``copy_streams`` (torch.cuda.Stream objects), each followed on its
+    stream by the store that sets the piece's flag."""
+    lib = _lib.load()
+    if not (x_host.is_pinned() and x_host.dtype == torch.float32 and x_host.is_contiguous()):
+        raise ValueError("x_host must be a contiguous pinned float32 CPU tensor")
+    _chk(x_dev, "x_dev", tuple(x_host.shape))
+    B, D = x_host.shape
+    arr = (C.c_void_p * len(copy_streams))(*[s.cuda_stream for s in copy_streams])
+    with torch.cuda.device(x_dev.device):
+        rc = lib.irbfn_upload_streamed(C.c_void_p(x_host.data_ptr()), _ptr(x_dev), B, D, _ptr(ready),
+                                       int(queries_per_flag), arr, len(copy_streams))
+    _lib.check(rc, "irbfn_upload_streamed")
+
+
 _ws_cache = {}
 
 

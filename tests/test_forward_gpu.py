@@ -257,14 +257,15 @@ def test_host_pipeline_variants_agree(cuda_device):
     xh = torch.from_numpy(x.copy()).pin_memory()
     yh = torch.empty((5000, 2)).pin_memory()
     ref = net.apply(dp, torch.from_numpy(x).to(cuda_device)).cpu()
-    for kw in (dict(), dict(copy_streams=2), dict(graph=True), dict(graph=True), dict(run_streams=2),
-               dict(run_streams=3, graph=True), dict(run_streams=3, graph=True)):
+    for kw in (dict(streamed=False), dict(), dict(streamed=True), dict(copy_streams=2), dict(graph=True), dict(graph=True),
+               dict(run_streams=2), dict(run_streams=3, graph=True), dict(run_streams=3, graph=True)):
         yh.zero_()
         net.apply_host(dp, xh, out=yh, chunk=2048, **kw)
         torch.cuda.synchronize()
-        if kw.get("run_streams", 1) == 1:
+        if kw.get("run_streams", 1) == 1 and not kw.get("streamed"):
             assert torch.equal(yh, ref), kw
-        else:   # several chunk kernels in flight run unsplit (one CTA per tile): another summation order
+        else:   # the streamed launch and several chunk kernels in flight run unsplit (one CTA per tile): another
+                # summation order than the split small-batch call behind `ref`
             assert torch.allclose(yh, ref, rtol=0, atol=2e-6 * float(ref.abs().max())), kw
     xh.mul_(0.5)                                      # new values, same buffers: the graph must pick them up
     ref2 = net.apply(dp, xh.to(cuda_device)).cpu()
@@ -272,6 +273,41 @@ def test_host_pipeline_variants_agree(cuda_device):
     torch.cuda.synchronize()
     assert torch.equal(yh, ref2)
     assert np.array_equal(net.apply_host(dp, x * 0.5, chunk=2048), ref2.numpy())
+
+
+def test_streamed_host_path_matches_the_device_resident_forward(cuda_device):
+    """irbfn_forward_streamed through apply_host: ONE launch whose query tiles wait for their chunk of the upload and
+    which stores y straight into pinned host memory.  Bit-identical to the unsplit device-resident forward; calling it
+    again with new values in the same buffers (flags cleared and re-armed) and with a pageable NumPy input."""
+    import os
+    from conftest import GOLDEN_DIR
+    from irbfn_b200.basis import gaussian, inverse_quadratic
+    from irbfn_b200.model import WCRBFNet, device_params
+    ops = _ops()
+    for name, B, chunk in (("c2_frenet_12x100.npz", 300 * 1024 + 333, 65536), ("dnmpc_4regions_iq.npz", 70001, 4096),
+                           ("c2b_frenet_1x1000_o10.npz", 33000, 1024)):
+        cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, name))
+        bf = gaussian if cfg["basis_func"] == "gaussian" else inverse_quadratic
+        net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], bf, cfg["num_regions"],
+                       cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"],
+                       cfg["delta"])
+        dp = device_params({"params": params}, cuda_device)
+        x = _big_queries(arr, B, cuda_device, 3).cpu()
+        xh = x.clone().pin_memory()
+        yh = torch.full((B, cfg["out_features"]), float("nan")).pin_memory()
+        rb, lin = dp["params"]["rbf_list"], dp["params"]["linear"]
+        dense = lambda xx: ops.forward(xx.to(cuda_device), rb["centers"], rb["log_sigs"], lin["kernel"], lin["bias"],
+                                       gd=_gd(cfg, cuda_device), basis=orc.BASIS_IDS[cfg["basis_func"]], split=False).cpu()
+        net.apply_host(dp, xh, out=yh, chunk=chunk, streamed=True)
+        torch.cuda.synchronize()
+        assert torch.equal(yh, dense(x)), name
+        xh.mul_(0.7)
+        yh.fill_(float("nan"))
+        net.apply_host(dp, xh, out=yh, chunk=chunk, streamed=True)
+        torch.cuda.synchronize()
+        assert torch.equal(yh, dense(xh)), name
+        y_np = net.apply_host(dp, x.numpy()[:5001], chunk=chunk, streamed=True)
+        assert np.array_equal(y_np, dense(x[:5001]).numpy()), name
 
 
 def test_forward_also_writes_the_gate_for_the_backward(cuda_device):
