@@ -269,11 +269,14 @@ def main():
     def lattice_step(i):
         _, yl = net.apply_lattice(params, axes_, fixed_)
         yh.copy_(yl, non_blocking=True)
-    ms_lat = timed(lattice_step, args.steps, args.warmup)
+    ms_lat_dl = timed(lattice_step, args.steps, args.warmup)
+    # the same with y stored by the kernel straight into the pinned host buffer (no download pass)
+    ms_lat = timed(lambda i: net.apply_lattice(params, axes_, fixed_, out=yh), args.steps, args.warmup)
     e2e["lattice_api"] = {"value": world * B / (ms_lat * 1e-3), "ms_per_step": ms_lat,
+                          "ms_per_step_with_download_pass": ms_lat_dl,
                           "h2d_bytes_per_step": int(sum(v.size for v in axes_.values()) * 4 + 32 + 64),
                           "d2h_bytes_per_step": int(yh.numel() * 4),
-                          "note": "WCRBFNet.apply_lattice: lattice built on the device (irbfn_lattice_queries)"}
+                          "note": "WCRBFNet.apply_lattice(out=pinned): lattice built on the device (irbfn_lattice_queries), y stored to host memory by the kernel"}
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -274,13 +274,31 @@ class WCRBFNet(_IrbfnModule):
         return _IrbfnFunction.apply(xd, centers, log_sigs, kernel, bias, None, self._gate_pack(device),
                                     self._basis, False)
 
-    def apply_lattice(self, params, axes, fixed, tol_abs: Optional[float] = None):
+    def apply_lattice(self, params, axes, fixed, tol_abs: Optional[float] = None, out=None):
         """The sweep of irbfn_vs_explicit*.ipynb cells 8-10 without moving the lattice over the host link:
         queries = meshgrid(axes, indexing="ij") with the other columns held at ``fixed``, generated on the device
         (``ops.lattice_queries``), then ``apply`` (or ``apply_sparse`` when ``tol_abs`` is given).
-        Returns (x, y), both CUDA tensors."""
+        Returns (x, y), both CUDA tensors -- or, with ``out`` (a pinned CPU tensor (B,O), O <= 16, dense evaluation),
+        y is stored by the kernel straight into that host buffer while it computes (no download pass; valid once the
+        current stream has been synchronised) and (x, out) is returned."""
         device = _default_device()
         x = ops.lattice_queries(axes, fixed, device)
+        if out is not None:
+            if tol_abs is not None or self.out_features > 16:
+                raise ValueError("out= needs the dense evaluation and at most 16 outputs")
+            p = _unwrap(params)
+            centers, log_sigs = self._rbf_leaves(p, device)
+            kernel, bias = _leaf(p["linear"]["kernel"], device), _leaf(p["linear"]["bias"], device)
+            key = ("ready1", str(device))
+            if key not in self._const:
+                self._const[key] = torch.zeros(2, dtype=torch.int32, device=device)
+            ready = self._const[key]          # [flag of the one piece = the whole batch, tile counter]
+            ready[0:1].fill_(1)
+            ready[1:2].zero_()
+            qpf = ((x.shape[0] + 1023) // 1024) * 1024
+            ops.forward_streamed(x, centers, log_sigs, kernel, bias, out, ready, qpf, gd=self._gate_pack(device),
+                                 basis=self._basis)
+            return x, out
         y = self.apply(params, x) if tol_abs is None else self.apply_sparse(params, x, tol_abs)
         return x, y
 

@@ -153,3 +153,33 @@ def test_lattice_queries_match_the_numpy_meshgrid(cuda_device):
         ref = lattice_queries(axes, fixed)
         got = ops.lattice_queries(axes, fixed, cuda_device).cpu().numpy()
         assert got.shape == ref.shape and np.array_equal(got, ref)
+
+
+def test_apply_lattice_into_a_pinned_host_buffer(cuda_device):
+    """apply_lattice(out=pinned): the kernel stores y straight into host memory; same values as the device-resident
+    evaluation of the same lattice (unsplit kernel: bit-identical), ragged last tile included."""
+    import os
+    from conftest import GOLDEN_DIR, load_golden
+    from irbfn_b200 import ops
+    from irbfn_b200.basis import gaussian
+    from irbfn_b200.model import WCRBFNet, device_params
+    cfg, params, _ = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                   cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"], cfg["delta"])
+    dp = device_params({"params": params}, cuda_device)
+    lo = [min(b) for b in cfg["lower_bounds"]]
+    hi = [max(b) for b in cfg["upper_bounds"]]
+    axes = {0: np.linspace(lo[0], hi[0], 37).astype(np.float32), 6: np.linspace(lo[6], hi[6], 31).astype(np.float32),
+            2: np.linspace(lo[2], hi[2], 5).astype(np.float32)}
+    fixed = np.zeros(8, np.float32)
+    fixed[4] = 4.0
+    B = 37 * 31 * 5
+    yh = torch.full((B, 2), float("nan")).pin_memory()
+    for _ in range(2):                                   # the flag / counter words are re-armed on every call
+        x, out = net.apply_lattice(dp, axes, fixed, out=yh)
+        torch.cuda.synchronize()
+        rb, lin = dp["params"]["rbf_list"], dp["params"]["linear"]
+        ref = ops.forward(x, rb["centers"], rb["log_sigs"], lin["kernel"], lin["bias"], gd=net._gate_pack(cuda_device),
+                          basis=0, split=False)
+        assert out is yh and torch.equal(yh, ref.cpu())
+        yh.fill_(float("nan"))
