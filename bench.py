@@ -507,9 +507,19 @@ def extras(net, params, cfg, dev, world, args):
     run4 = lambda: ops.backward(x4, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
                                 dy4, gd=gd, basis=0, grad_mask=ops.GRAD_X)
     ms4 = timed(run4, max(3, args.steps // 2), 3)
+    # gate-sparse: queries binned by their non-negligible gate intervals, regions skipped per warp (gate_tol = 2^-24)
+    dx_dense = run4()["x"].clone()
+    run4s = lambda: ops.backward(x4, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
+                                 dy4, gd=gd, basis=0, grad_mask=ops.GRAD_X, gate_tol=2.0 ** -24)
+    ms4s = timed(run4s, max(3, args.steps // 2), 3)
+    dev4 = float((run4s()["x"] - dx_dense).norm() / dx_dense.norm())
+    del dx_dense
     res["input_grad_C4"] = {"queries_per_gpu": B4, "scaling": "weak", "ms_vjp_dx": ms4,
                             "queries_per_s": world * B4 / (ms4 * 1e-3),
-                            "algorithmic_tflops": (R * K * (5 * D + 7) + 2 * K * O) * B4 / (ms4 * 1e-3) / 1e12}
+                            "algorithmic_tflops": (R * K * (5 * D + 7) + 2 * K * O) * B4 / (ms4 * 1e-3) / 1e12,
+                            "gate_sparse": {"gate_tol": 2.0 ** -24, "ms_vjp_dx_incl_binning": ms4s,
+                                            "rel_l2_vs_dense": dev4}}
+    tail["c4"] = {"queries_per_gpu": B4, "ms_vjp_dx": ms4, "ms_vjp_dx_gate_sparse": ms4s, "n_gpus": world}
     # 8f rank 2: one-pass Jacobian dy/dx (B,O,D) on the C4 queries, against O one-hot VJP launches (jacrev)
     W_, b_ = p["linear"]["kernel"], p["linear"]["bias"]
     msj = timed(lambda: ops.jacobian(x4, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], W_, gd=gd, basis=0),

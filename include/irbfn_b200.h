@@ -240,7 +240,10 @@ int irbfn_backward(const float* x, const float* centers, const float* log_sigs, 
  * (dcenters, dlog_sigs, dW) leave out the terms of every (query b, region r) pair whose gate gamma[b,r] <= gate_tol;
  * each such term of jax.value_and_grad(loss_fn) (scripts/train_nmpc.py:297) carries the factor gamma[b,r], so
  *     |d theta - d theta(dense)| <= gate_tol * sum over dropped (b,r) of |d(phi_rk dh_bk)/d theta|,
- * and gate_tol = 0 drops only gates that are exactly 0 (bit-identical sums).  dbias, dx and dgate are not affected.
+ * and gate_tol = 0 drops only gates that are exactly 0 (bit-identical sums).  dbias and dgate are not affected.
+ * dx (tanh gate): the queries are binned by their set of non-negligible gate intervals (as irbfn_forward_sparse does)
+ * and a warp skips the regions whose gate is <= gate_tol for all of its 128 queries; every dropped term of dx, the
+ * gate path included, carries the factor gamma, so dx moves by the order of gate_tol too.
  * The tanh gate of the shipped multi-region shapes is > 2^-24 for 4-5 of 12 regions on uniformly drawn queries.
  * The kernel's threads own (region, kernel) pairs and a query is a broadcast operand, so the skip is one
  * warp-uniform vote per (warp, query): no binning pass, same fixed summation order (deterministic).  Shapes without a

@@ -35,7 +35,7 @@ FEATURE_COUNTS = (4, 5, 6, 7, 8)
 def _units():
     units = [("irbfn_api.cu", [], "irbfn_api.o"), ("irbfn_dynamics.cu", [], "irbfn_dynamics.o"),
              ("irbfn_table.cu", [], "irbfn_table.o"), ("irbfn_optim.cu", [], "irbfn_optim.o")]
-    for name in ("irbfn_fwd_inst.cu", "irbfn_fwdm_inst.cu", "irbfn_bwd_x_inst.cu", "irbfn_bwd_p_inst.cu", "irbfn_bwd_ps_inst.cu", "irbfn_bwd_pw_inst.cu",
+    for name in ("irbfn_fwd_inst.cu", "irbfn_fwdm_inst.cu", "irbfn_bwd_x_inst.cu", "irbfn_bwd_xs_inst.cu", "irbfn_bwd_p_inst.cu", "irbfn_bwd_ps_inst.cu", "irbfn_bwd_pw_inst.cu",
                  "irbfn_jac_inst.cu"):
         if not os.path.exists(os.path.join(CSRC, name)):
             continue

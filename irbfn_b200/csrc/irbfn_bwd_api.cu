@@ -19,6 +19,13 @@ int launch_bwd_ps_d5(const BwdPArgs&, int, int, int, int, int, size_t, cudaStrea
 int launch_bwd_ps_d6(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_ps_d7(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_ps_d8(const BwdPArgs&, int, int, int, int, int, size_t, cudaStream_t);
+int launch_bwd_xs_d4(const BwdXArgs&, int, int, int, size_t, cudaStream_t);   // gate-sparse query-side backward
+int launch_bwd_xs_d5(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
+int launch_bwd_xs_d6(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
+int launch_bwd_xs_d7(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
+int launch_bwd_xs_d8(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
+size_t sparse_bin_workspace_bytes(long long B, int num_bounds);                // irbfn_sparse.cu
+int sparse_bin_queries(const float*, const GateDev&, float, long long, int, int, void*, const int**, cudaStream_t);
 int launch_bwd_pw_d4(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_pw_d5(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_pw_d6(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
@@ -236,8 +243,10 @@ __global__ void __launch_bounds__(256) dh_kernel(const float* __restrict__ dy, c
     dh[i] = acc;
 }
 
+constexpr int kSparseBoundsMax = 1024;   // gate intervals the sparse query-side pass is sized for (else it runs dense)
+
 struct BwdLayout {
-    size_t gate_off, part_off, partdb_off, dgate_off, dh_off, total;
+    size_t gate_off, part_off, partdb_off, dgate_off, dh_off, sparse_off, total;
     BwdPPlan pplan;
     size_t max_part_floats;
     int need_p, need_x;
@@ -284,6 +293,8 @@ static bool bwd_layout(int64_t B, int R, int K, int D, int O, unsigned mask, int
     if (L->need_x) {
         if (tanh_gate && (mask & IRBFN_GRAD_X)) { L->dgate_off = off; off = align256(off + (size_t)B * R * sizeof(float)); }
         if (O > 16) { L->dh_off = off; off = align256(off + (size_t)B * K * sizeof(float)); }
+        // binning scratch of the gate-sparse query-side pass (irbfn_backward_sparse): 8 bytes per query + histogram
+        if (tanh_gate && (mask & IRBFN_GRAD_X)) { L->sparse_off = off; off = align256(off + sparse_bin_workspace_bytes(B, kSparseBoundsMax)); }
     }
     L->total = off;
     return true;
@@ -521,7 +532,23 @@ static int backward_impl(const float* x, const float* centers, const float* log_
         const long long tiles = (B + BwdXShape::TQ - 1) / BwdXShape::TQ;
         a.num_tiles = (int)tiles;
         const int grid = (int)(tiles < sms ? tiles : sms);
-        int e;
+        int e = -1;
+        if (gate_thr >= 0.0f && gd != nullptr && (grad_mask & IRBFN_GRAD_X) && R > 1 && plan.RC <= 64 &&
+            gdev.num_bounds <= kSparseBoundsMax && B <= 0x7fffffffll) {
+            // gate-sparse: bin the queries by their set of non-negligible gate intervals, then the SPARSE instantiation
+            const int* perm = nullptr;
+            const int be = sparse_bin_queries(x, gdev, gate_thr, B, D, sms, ws + L.sparse_off, &perm, st);
+            if (be != 0) return note_cuda_error("sparse binning (backward)", be);
+            a.perm = perm;
+            a.gate_thr = gate_thr;
+            switch (DT) {
+                case 4: e = launch_bwd_xs_d4(a, OT, basis, grid, plan.smem_bytes, st); break;
+                case 5: e = launch_bwd_xs_d5(a, OT, basis, grid, plan.smem_bytes, st); break;
+                case 6: e = launch_bwd_xs_d6(a, OT, basis, grid, plan.smem_bytes, st); break;
+                case 7: e = launch_bwd_xs_d7(a, OT, basis, grid, plan.smem_bytes, st); break;
+                default: e = launch_bwd_xs_d8(a, OT, basis, grid, plan.smem_bytes, st); break;
+            }
+        } else
         switch (DT) {
             case 4: e = launch_bwd_x_d4(a, OT, basis, grid, plan.smem_bytes, st); break;
             case 5: e = launch_bwd_x_d5(a, OT, basis, grid, plan.smem_bytes, st); break;

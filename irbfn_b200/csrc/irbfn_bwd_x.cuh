@@ -38,6 +38,10 @@ struct BwdXArgs {
     int num_tiles;
     int stage_once;
     int fuse_gate;          // 1: tanh gate, S <= 4: d gamma is folded into dx inside this kernel
+    // ---- read by the SPARSE instantiations only (irbfn_backward_sparse); behind the dense fields ----
+    const int* perm;        // (B): queries are visited in this order (grouped by their set of non-negligible regions)
+    float gate_thr;         // a (query, region) pair with gamma <= gate_thr is dropped; a warp skips the regions
+                            // that are dropped for all of its 128 queries
 };
 
 struct BwdXShape {
@@ -46,7 +50,11 @@ struct BwdXShape {
     static __host__ __device__ constexpr int tile_floats(int D) { return (D + 2) * 4; }
 };
 
-template <int D, int OT, int BASIS>
+// SPARSE = 1: gate-sparse, region-binned evaluation exactly as the forward's (irbfn_fwd_modes.cuh, irbfn_sparse.cu):
+// rows gathered and results scattered through perm, the drop rule applied per query, the hot loop run over the warp's
+// active regions only.  Every dropped term of dx carries the factor gamma (the gate path too: d gamma / dx = gamma *
+// d log gamma / dx), so |dx - dx(dense)| is of the order of gate_thr.  Tanh gate, at most 64 regions per stage.
+template <int D, int OT, int BASIS, int SPARSE = 0>
 __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const BwdXArgs a) {
     constexpr int NT = BwdXShape::NT, Q = BwdXShape::Q, TQ = BwdXShape::TQ, KT = BwdXShape::KT;
     constexpr int OTS = OT > 0 ? OT : 1;
@@ -71,17 +79,35 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
         const long long q0 = (long long)tile * TQ + (long long)tid * Q;
 
         float2 x2[2][D];
-        load_queries4<D>(a.x, q0, a.B, a.Dsrc, x2);
+        long long qi[Q];                      // the rows this thread evaluates (SPARSE: permuted order), -1 = none
+#pragma unroll
+        for (int i = 0; i < Q; ++i) {
+            if (SPARSE) qi[i] = q0 + i < a.B ? (long long)__ldg(a.perm + q0 + i) : -1ll;
+            else qi[i] = q0 + i < a.B ? q0 + i : -1ll;
+        }
+        if (SPARSE) {
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+#pragma unroll
+                for (int j = 0; j < D; ++j) {
+                    x2[p][j].x = (qi[2 * p] >= 0 && j < a.Dsrc) ? __ldg(a.x + qi[2 * p] * a.Dsrc + j) : 0.f;
+                    x2[p][j].y = (qi[2 * p + 1] >= 0 && j < a.Dsrc) ? __ldg(a.x + qi[2 * p + 1] * a.Dsrc + j) : 0.f;
+                }
+            }
+        } else {
+            load_queries4<D>(a.x, q0, a.B, a.Dsrc, x2);
+        }
         // cotangent rows, packed over the query pair
         float2 dy2[2][OTS];
         if (OT > 0) {
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
-                const long long qa = q0 + 2 * p, qb = qa + 1;
+                const long long qa = SPARSE ? qi[2 * p] : q0 + 2 * p, qb = SPARSE ? qi[2 * p + 1] : qa + 1;
+                const bool va = SPARSE ? qa >= 0 : qa < a.B, vb = SPARSE ? qb >= 0 : qb < a.B;
 #pragma unroll
                 for (int o = 0; o < OT; ++o) {
-                    dy2[p][o].x = (qa < a.B && o < O) ? __ldg(a.dy + qa * O + o) : 0.f;
-                    dy2[p][o].y = (qb < a.B && o < O) ? __ldg(a.dy + qb * O + o) : 0.f;
+                    dy2[p][o].x = (va && o < O) ? __ldg(a.dy + qa * O + o) : 0.f;
+                    dy2[p][o].y = (vb && o < O) ? __ldg(a.dy + qb * O + o) : 0.f;
                 }
             }
         }
@@ -113,11 +139,27 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                     g.w = (q0 + 3 < a.B) ? __ldg(a.gate_ext + (q0 + 3) * R + r0 + rr) : 0.f;
                     gcol[rr * NT] = g;
                 }
+            } else if (SPARSE) {
+                gate_columns_rows(a.gd, a.x, qi, a.Dsrc, r0, rc, gcol, NT);
             } else {
                 gate_columns(a.gd, a.x, q0, a.B, a.Dsrc, r0, rc, gcol, NT);
             }
             if (want_dg)
                 for (int rr = 0; rr < rc; ++rr) dgcol[rr * NT] = make_float4(0.f, 0.f, 0.f, 0.f);
+            // ---- SPARSE: the drop rule per query, then the regions this warp still needs ----
+            unsigned long long wmask = 0ull;
+            if (SPARSE) {
+                for (int rr = 0; rr < rc; ++rr) {
+                    float4 g = gcol[rr * NT];
+                    g.x = g.x > a.gate_thr ? g.x : 0.f;
+                    g.y = g.y > a.gate_thr ? g.y : 0.f;
+                    g.z = g.z > a.gate_thr ? g.z : 0.f;
+                    g.w = g.w > a.gate_thr ? g.w : 0.f;
+                    gcol[rr * NT] = g;
+                    const bool act = fmaxf(fmaxf(g.x, g.y), fmaxf(g.z, g.w)) > 0.f;
+                    if (__any_sync(0xffffffffu, act)) wmask |= 1ull << rr;
+                }
+            }
 
             for (int kch = 0; kch < n_kch; ++kch) {
                 const int k0 = kch * KC;
@@ -218,6 +260,15 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                     }
                     if (want_dg) {
                         float4 d = dgcol[rrp * NT];
+                        if (SPARSE) {
+                            // a (query, region) pair that the drop rule removed contributes nothing to the gate path
+                            // either, whether or not the query's warp evaluated the region for other queries: a
+                            // query's gradient must not depend on which queries share its warp
+                            dg2[0].x = gp[0].x > 0.f ? dg2[0].x : 0.f;
+                            dg2[0].y = gp[0].y > 0.f ? dg2[0].y : 0.f;
+                            dg2[1].x = gp[1].x > 0.f ? dg2[1].x : 0.f;
+                            dg2[1].y = gp[1].y > 0.f ? dg2[1].y : 0.f;
+                        }
                         d.x += dg2[0].x; d.y += dg2[0].y; d.z += dg2[1].x; d.w += dg2[1].y;
                         dgcol[rrp * NT] = d;
                     }
@@ -249,9 +300,9 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                             if (k < K) {
 #pragma unroll
                                 for (int p = 0; p < 2; ++p) {
-                                    const long long qa = q0 + 2 * p, qb = qa + 1;
-                                    dh2[kk][p].x = qa < a.B ? __ldg(a.dhidden + qa * K + k) : 0.f;
-                                    dh2[kk][p].y = qb < a.B ? __ldg(a.dhidden + qb * K + k) : 0.f;
+                                    const long long qa = qi[2 * p], qb = qi[2 * p + 1];
+                                    dh2[kk][p].x = qa >= 0 ? __ldg(a.dhidden + qa * K + k) : 0.f;
+                                    dh2[kk][p].y = qb >= 0 ? __ldg(a.dhidden + qb * K + k) : 0.f;
                                 }
                             }
                         }
@@ -268,6 +319,41 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                 };
 
                 const size_t rstride = (size_t)KCT * TR;
+                if (SPARSE) {
+                    // the same pipeline over the warp's active regions only (warp-uniform trip counts; the CTA's
+                    // barriers all sit in the staging above, which every warp still joins)
+                    if (wmask != 0ull) {
+                        const int rr0 = __ffsll((long long)wmask) - 1;
+                        const unsigned long long rest = wmask & (wmask - 1ull);
+                        for (int kt = 0; kt < kcp; kt += KT) {
+                            const float4* rec0 = stage4 + (size_t)(kt >> 2) * TR;
+                            {
+                                const float4* rec = rec0 + (size_t)rr0 * rstride;
+                                const float4 g4 = gcol[rr0 * NT];
+                                float2 acc[KT][2];
+                                distances(rec, acc);
+                                finish();
+                                load_dh(kt);
+                                scale(rec, acc, g4, rr0);
+                            }
+                            unsigned long long m = rest;
+                            while (m) {
+                                const int rr = __ffsll((long long)m) - 1;
+                                m &= m - 1ull;
+                                const float4* rec = rec0 + (size_t)rr * rstride;
+                                const float4 g4 = gcol[rr * NT];
+                                float2 acc[KT][2];
+                                distances(rec, acc);
+                                finish();
+                                scale(rec, acc, g4, rr);
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) mufu(i);
+                        finish();
+                    }
+                    continue;
+                }
                 for (int kt = 0; kt < kcp; kt += KT) {
                     const float4* rec = stage4 + (size_t)(kt >> 2) * TR;
                     {   // first region of the tile (peeled): the previous step belongs to tile kt - KT,
@@ -300,6 +386,7 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                 const int S = a.gd.S;
                 const int rlim = min(rc, a.gd.num_ranges - r0);
                 for (int rr = 0; rr < rlim; ++rr) {
+                    if (SPARSE && !((wmask >> rr) & 1ull)) continue;   // d gamma of a skipped region is 0
                     const float4 dgv = dgcol[rr * NT];
                     float4 f[BwdXShape::MAX_FUSED_S], fd[BwdXShape::MAX_FUSED_S];
 #pragma unroll
@@ -343,10 +430,10 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
             } else if (a.dgate != nullptr) {
                 for (int rr = 0; rr < rc; ++rr) {
                     const float4 d = dgcol[rr * NT];
-                    if (q0 + 0 < a.B) a.dgate[(q0 + 0) * R + r0 + rr] = d.x;
-                    if (q0 + 1 < a.B) a.dgate[(q0 + 1) * R + r0 + rr] = d.y;
-                    if (q0 + 2 < a.B) a.dgate[(q0 + 2) * R + r0 + rr] = d.z;
-                    if (q0 + 3 < a.B) a.dgate[(q0 + 3) * R + r0 + rr] = d.w;
+                    if (qi[0] >= 0) a.dgate[qi[0] * R + r0 + rr] = d.x;
+                    if (qi[1] >= 0) a.dgate[qi[1] * R + r0 + rr] = d.y;
+                    if (qi[2] >= 0) a.dgate[qi[2] * R + r0 + rr] = d.z;
+                    if (qi[3] >= 0) a.dgate[qi[3] * R + r0 + rr] = d.w;
                 }
             }
         }
@@ -355,7 +442,7 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
         if (a.dx != nullptr) {
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
-                const long long qa = q0 + 2 * p, qb = qa + 1;
+                const long long qa = qi[2 * p], qb = qi[2 * p + 1];
 #pragma unroll
                 for (int j = 0; j < D; ++j) {
                     float2 r = fma2(x2[p][j], sw[p], dxn[p][j]);
@@ -364,8 +451,8 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
                         r.y += p == 0 ? dxg[j].y : dxg[j].w;
                     }
                     if (j < a.Dsrc) {
-                        if (qa < a.B) a.dx[qa * a.Dsrc + j] = r.x;
-                        if (qb < a.B) a.dx[qb * a.Dsrc + j] = r.y;
+                        if (qa >= 0) a.dx[qa * a.Dsrc + j] = r.x;
+                        if (qb >= 0) a.dx[qb * a.Dsrc + j] = r.y;
                     }
                 }
             }
@@ -373,16 +460,16 @@ __global__ void __launch_bounds__(BwdXShape::NT, 1) irbfn_bwd_x_kernel(const Bwd
     }
 }
 
-template <int D, int OT>
+template <int D, int OT, int SPARSE = 0>
 inline int launch_bwd_x_ot(const BwdXArgs& a, int basis, int grid, size_t smem, cudaStream_t st) {
     cudaError_t e;
     if (basis == IRBFN_BASIS_GAUSSIAN) {
-        auto kern = irbfn_bwd_x_kernel<D, OT, IRBFN_BASIS_GAUSSIAN>;
+        auto kern = irbfn_bwd_x_kernel<D, OT, IRBFN_BASIS_GAUSSIAN, SPARSE>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
         kern<<<grid, BwdXShape::NT, smem, st>>>(a);
     } else {
-        auto kern = irbfn_bwd_x_kernel<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC>;
+        auto kern = irbfn_bwd_x_kernel<D, OT, IRBFN_BASIS_INVERSE_QUADRATIC, SPARSE>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
         kern<<<grid, BwdXShape::NT, smem, st>>>(a);
@@ -399,6 +486,20 @@ inline int launch_bwd_x(const BwdXArgs& a, int OT, int basis, int grid, size_t s
         case 8: return launch_bwd_x_ot<D, 8>(a, basis, grid, smem, st);
         case 10: return launch_bwd_x_ot<D, 10>(a, basis, grid, smem, st);
         case 16: return launch_bwd_x_ot<D, 16>(a, basis, grid, smem, st);
+        default: return (int)cudaErrorInvalidValue;
+    }
+}
+
+// gate-sparse instantiations (irbfn_bwd_xs_inst.cu)
+template <int D>
+inline int launch_bwd_x_sparse(const BwdXArgs& a, int OT, int basis, int grid, size_t smem, cudaStream_t st) {
+    switch (OT) {
+        case 0: return launch_bwd_x_ot<D, 0, 1>(a, basis, grid, smem, st);
+        case 2: return launch_bwd_x_ot<D, 2, 1>(a, basis, grid, smem, st);
+        case 4: return launch_bwd_x_ot<D, 4, 1>(a, basis, grid, smem, st);
+        case 8: return launch_bwd_x_ot<D, 8, 1>(a, basis, grid, smem, st);
+        case 10: return launch_bwd_x_ot<D, 10, 1>(a, basis, grid, smem, st);
+        case 16: return launch_bwd_x_ot<D, 16, 1>(a, basis, grid, smem, st);
         default: return (int)cudaErrorInvalidValue;
     }
 }

@@ -252,7 +252,47 @@ SparseLayout sparse_layout(int64_t B, int num_bounds) {
     return L;
 }
 
+__global__ void set_thr_kernel(float* thr, float v) { *thr = v; }
+
 }  // namespace
+
+// Binning for the other gate-sparse kernels (irbfn_backward_sparse's query-side pass): perm = the queries grouped by
+// their set of gate intervals whose factor exceeds thr.  Workspace of sparse_bin_workspace_bytes(B, num_bounds) bytes;
+// returns the device pointer of perm (inside the workspace) through perm_out.  Returns 0 or a cudaError_t.
+size_t sparse_bin_workspace_bytes(long long B, int num_bounds) { return sparse_layout(B, num_bounds).total; }
+
+int sparse_bin_queries(const float* x, const GateDev& gdev, float thr_value, long long B, int D, int sms, void* workspace,
+                       const int** perm_out, cudaStream_t st) {
+    const SparseLayout L = sparse_layout(B, gdev.num_bounds);
+    char* ws = (char*)workspace;
+    float* thr = (float*)(ws + L.thr_off);
+    float* edge = (float*)(ws + L.edge_off);
+    unsigned* hist = (unsigned*)(ws + L.hist_off);
+    unsigned* keys = (unsigned*)(ws + L.keys_off);
+    int* perm = (int*)(ws + L.perm_off);
+    if (cudaMemsetAsync(ws + L.hist_off, 0, (size_t)L.nb * sizeof(unsigned), st) != cudaSuccess) return (int)cudaGetLastError();
+    set_thr_kernel<<<1, 1, 0, st>>>(thr, thr_value);
+    sparse_edges_kernel<<<1, 64, 0, st>>>(gdev, thr, edge);
+    const size_t edge_bytes = 2 * (size_t)gdev.num_bounds * sizeof(float);
+    if (L.nb <= kBlockBins && (size_t)L.nb * sizeof(unsigned) + edge_bytes <= 48 * 1024) {
+        long long nblk2 = (B + 2047) / 2048;
+        if (nblk2 > 4ll * sms) nblk2 = 4ll * sms;
+        const long long per = (B + nblk2 - 1) / nblk2;
+        sparse_key_block_kernel<<<(unsigned)nblk2, 256, (size_t)L.nb * sizeof(unsigned) + edge_bytes, st>>>(
+            x, gdev, edge, keys, hist, B, D, L.key_bits, per);
+        sparse_scan_kernel<<<1, 1024, 0, st>>>(hist, L.nb);
+        sparse_scatter_block_kernel<<<(unsigned)nblk2, 256, (size_t)L.nb * sizeof(unsigned), st>>>(keys, hist, perm, B, L.nb, per);
+    } else {
+        if (edge_bytes > 48 * 1024) return (int)cudaErrorInvalidValue;
+        const int nblk = (int)((B + 255) / 256 < (long long)sms * 16 ? (B + 255) / 256 : (long long)sms * 16);
+        sparse_key_kernel<<<nblk, 256, edge_bytes, st>>>(x, gdev, edge, keys, hist, B, D, L.key_bits);
+        sparse_scan_kernel<<<1, 1024, 0, st>>>(hist, L.nb);
+        sparse_scatter_kernel<<<nblk, 256, 0, st>>>(keys, hist, perm, B);
+    }
+    *perm_out = perm;
+    return (int)cudaGetLastError();
+}
+
 }  // namespace irbfn
 
 using namespace irbfn;

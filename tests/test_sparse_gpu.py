@@ -136,14 +136,15 @@ def test_sparse_backward_matches_reference_gradients_on_shipped_checkpoints(path
         assert _rel_l2(g0[leaf].cpu().numpy(), arr[key]) < GRAD_TOL, leaf
 
 
-@pytest.mark.parametrize("shape", [(1023, 3, 7, 4, 2), (5000, 12, 100, 8, 2), (3000, 27, 30, 8, 10), (2049, 64, 40, 6, 16),
-                                   (777, 5, 33, 5, 4), (4000, 130, 6, 7, 18)],
-                         ids=lambda s: "B%d_R%d_K%d_D%d_O%d" % s)
+@pytest.mark.parametrize("shape", [(1023, 3, 7, 4, 2, 3), (5000, 12, 100, 8, 2, 8), (3000, 27, 30, 8, 10, 3), (2049, 64, 40, 6, 16, 3),
+                                   (777, 5, 33, 5, 4, 5), (4000, 130, 6, 7, 18, 3)],
+                         ids=lambda s: "B%d_R%d_K%d_D%d_O%d_S%d" % s)
 def test_sparse_backward_matches_dense_oracle_with_sharp_gates(shape, cuda_device):
-    """Uniform queries, sharp gates (most (query, region) pairs are skipped), narrow and wide outputs, odd K."""
+    """Uniform queries, sharp gates (most (query, region) pairs are skipped), narrow and wide outputs, odd K; gates with
+    up to 4 split dimensions (folded into dx inside the kernel) and more (gate_bwd_kernel); 130 regions (dense dx)."""
     ops = _ops()
-    B, R, K, D, O = shape
-    cfg, p, x = _synthetic(43, B, R, K, D, O, S=min(3, D), nb=(4, 3, 2))
+    B, R, K, D, O, S = shape
+    cfg, p, x = _synthetic(43, B, R, K, D, O, S=S, nb=(4, 3, 2))
     cfg["delta"] = [40.0] * len(cfg["delta"])
     dev = cuda_device
     rng = np.random.default_rng(5)
@@ -155,9 +156,17 @@ def test_sparse_backward_matches_dense_oracle_with_sharp_gates(shape, cuda_devic
     for basis in (0, 1):
         ref = orc.backward(x64, p["centers"], p["log_sigs"], p["kernel"], p["bias"], gamma, dy.astype(np.float64), basis)
         args = (_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev), _t(dy, dev))
-        g = ops.backward(*args, gd=_gd(cfg, dev), basis=basis, gate_tol=GATE_TOL)
+        g = ops.backward(*args, gd=_gd(cfg, dev), basis=basis, gate_tol=GATE_TOL, grad_mask=ops.GRAD_PARAMS | ops.GRAD_X)
         for leaf in ("centers", "log_sigs", "kernel", "bias"):
             assert _rel_l2(g[leaf].cpu().numpy(), ref[leaf]) < GRAD_TOL, (basis, leaf)
+        # dx: binned queries, regions skipped per warp; the full input gradient (RBF layers + gate path)
+        cfg["basis_func"] = "gaussian" if basis == 0 else "inverse_quadratic"
+        params = {"rbf_list": {"centers": p["centers"], "log_sigs": p["log_sigs"]},
+                  "linear": {"kernel": p["kernel"], "bias": p["bias"]}}
+        refx = orc.wcrbf_vjp(x64, params, cfg, dy.astype(np.float64))["x"]
+        assert _rel_l2(g["x"].cpu().numpy(), refx) < GRAD_TOL, basis
+        g2 = ops.backward(*args, gd=_gd(cfg, dev), basis=basis, gate_tol=GATE_TOL, grad_mask=ops.GRAD_X)
+        assert torch.equal(g["x"], g2["x"])                # the binning order cannot change a query's gradient
         # an externally supplied gate (what a training step hands over from irbfn_forward_gate) takes the same path
         gate = ops.region_gate(_t(x, dev), _gd(cfg, dev), R)
         ge = ops.backward(*args, gate=gate, basis=basis, gate_tol=GATE_TOL)
