@@ -95,10 +95,10 @@ class _IrbfnFunction(torch.autograd.Function):
         dout = dout.contiguous()
         if ctx.want_hidden:
             g = ops.backward(x, centers, log_sigs, None, None, dhidden=dout, gate=gate, gd=ctx.gd,
-                             basis=ctx.basis, grad_mask=mask)
+                             basis=ctx.basis, grad_mask=mask, gate_tol=getattr(ctx.gd, "gate_tol", None))
         else:
             g = ops.backward(x, centers, log_sigs, kernel, dout, gate=gate, gd=ctx.gd, basis=ctx.basis,
-                             grad_mask=mask)
+                             grad_mask=mask, gate_tol=getattr(ctx.gd, "gate_tol", None))
         return (g.get("x") if need[0] else None, g.get("centers") if need[1] else None,
                 g.get("log_sigs") if need[2] else None, g.get("kernel") if need[3] else None,
                 g.get("bias") if need[4] else None, g.get("gate") if need[5] else None, None, None, None)
@@ -181,6 +181,9 @@ class _IrbfnModule:
                 raise ValueError("activation_idx is empty: the tanh gate needs at least one split dimension")
             self._packs[key] = ops.GatePack(self.lower_bounds[:S], self.upper_bounds[:S], self.delta[:S],
                                             [r[:S] for r in self.dimension_ranges], device)
+        # None: dense VJP.  >= 0: autograd through apply() uses the gate-sparse VJP (irbfn_backward_sparse): terms of
+        # (query, region) pairs whose gate is <= gate_tol are left out (set ``module.gate_tol = 2.0 ** -24``)
+        self._packs[key].gate_tol = getattr(self, "gate_tol", None)
         return self._packs[key]
 
     def _fixed(self, name, device):

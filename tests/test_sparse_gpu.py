@@ -185,3 +185,33 @@ def test_sparse_backward_errors(cuda_device):
         ops.backward(*args, gd=_gd(cfg, dev), basis=0, gate_tol=-1.0)
     with pytest.raises(IrbfnError):
         ops.backward(*args, gd=_gd(cfg, dev), basis=0, gate_tol=float("nan"))
+
+
+def test_module_autograd_uses_the_sparse_vjp_when_gate_tol_is_set(cuda_device):
+    """torch.autograd.grad through WCRBFNet.apply (the stand-in for jax.grad through the Flax module): with
+    ``module.gate_tol`` set the custom VJP is irbfn_backward_sparse; gradients agree with the dense VJP."""
+    from conftest import GOLDEN_DIR
+    from irbfn_b200.basis import gaussian
+    from irbfn_b200.model import WCRBFNet, device_params
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                   cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"], cfg["delta"])
+    dp = device_params({"params": params}, cuda_device)
+    leaves = [dp["params"]["rbf_list"]["centers"], dp["params"]["rbf_list"]["log_sigs"], dp["params"]["linear"]["kernel"]]
+    for t in leaves:
+        t.requires_grad_(True)
+    x = torch.tensor(np.tile(arr["x"], (8, 1)).astype(np.float32), device=cuda_device, requires_grad=True)
+
+    def grads():
+        y = net.apply(dp, x)
+        return torch.autograd.grad((y * y).mean(), leaves + [x])
+
+    dense = grads()
+    net.gate_tol = GATE_TOL
+    sparse = grads()
+    net.gate_tol = None
+    for a, b in zip(sparse, dense):
+        assert _rel_l2(a.cpu().numpy(), b.cpu().numpy()) < 1e-5
+    again = grads()
+    for a, b in zip(again, dense):
+        assert torch.equal(a, b)                      # switching it off restores the dense VJP
