@@ -342,6 +342,23 @@ def main():
             out["parity_check"] = {"max_abs_err_over_max_abs": float(np.abs(y_gpu - y_cpu).max() / np.abs(y_cpu).max()),
                                    "against": "C oracle float32, same %d queries" % sample}
         out.update(tail)      # compact c3 / c5 / dp_parity objects LAST: they survive a truncated tail of the line
+        if tail:
+            # ... and one flat summary of them at the very end (a 1,500-character tail of the line always holds it)
+            r4 = lambda v: None if v is None else float("%.4g" % v)
+            c3, o10, c1s, c4, c5, dp = (tail.get(k) or {} for k in ("c3", "c3_o10_fullint", "c3_c1shape", "c4", "c5", "dp_parity"))
+            sp = lambda d: (d.get("gate_sparse_vjp") or {}).get("ms_graph")
+            out["summary"] = {
+                "n_gpus": world, "fwd_ms": r4(ms), "e2e_ms": r4(ms_e2e),
+                "c3_ms_graph": r4(c3.get("ms_graph")), "c3_ms_graph_nccl": r4(c3.get("ms_graph_nccl")),
+                "c3_ms_graph_gate_sparse": r4(sp(c3)), "c3_ms_kernels_this_rank": r4(c3.get("ms_kernels_this_rank")),
+                "c3_ms_nccl_allreduce_alone": r4(c3.get("ms_nccl_allreduce_alone")), "c3_allreduce": c3.get("allreduce"),
+                "dp_parity_rel_l2": r4(dp.get("rel_l2_max_over_leaves")), "dp_parity_ok": dp.get("ok"),
+                "c1shape_ms_graph": r4(c1s.get("ms_graph")), "o10_ms_graph": r4(o10.get("ms_graph")),
+                "o10_ms_graph_gate_sparse": r4(sp(o10)), "c4_ms": r4(c4.get("ms_vjp_dx")),
+                "c4_ms_gate_sparse": r4(c4.get("ms_vjp_dx_gate_sparse")), "c5_fwd_ms_per_2p24": r4(c5.get("fwd_ms_per_2p24")),
+                "c5_fwd_ms_gate_sparse": r4(c5.get("fwd_gate_sparse_ms_per_2p24")),
+                "c5_fwd_vjp_ms_per_2p22": r4(c5.get("fwd_vjp_ms_per_2p22")),
+                "c5_fwd_vjp_ms_gate_sparse": r4(c5.get("fwd_vjp_gate_sparse_ms_per_2p22"))}
         emit(out)
     elif not args.no_extras:
         extras(net, params, cfg, dev, world, args)   # collectives inside: every rank takes part
