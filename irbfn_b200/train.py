@@ -252,8 +252,13 @@ def _local_grad(state: TrainState, x: torch.Tensor, y: torch.Tensor, gb: int, lo
         state.loss_terms = terms          # [pred_loss, int_loss] of this shard (device)
         lval = terms.sum()
     else:
-        lv, dy = ops.prediction_loss(y_pred, y, gb, loss)     # one launch; loss_and_cotangent is its torch spelling
-        lval = lv[0]
+        # one launch; loss_and_cotangent is its torch spelling.  The loss lands directly behind the gradient in the
+        # buffer the collective reduces: it rides along, still one collective, no concat, no copy
+        n = state.grad.numel()
+        lv, dy = ops.prediction_loss(y_pred, y, gb, loss, loss=state._grad_src[n:n + 1])
+        ops.backward(x, centers, log_sigs, v["kernel"], dy, gate=state.gate_buf, basis=m._basis,
+                     grad_mask=state.mask, flat_out=state._grad_src[:n], gate_tol=state.gate_tol)
+        return lv[0]
     n = state.grad.numel()
     ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gate=state.gate_buf, basis=m._basis,
                  grad_mask=state.mask, flat_out=state._grad_src[:n], gate_tol=state.gate_tol)

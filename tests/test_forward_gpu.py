@@ -382,7 +382,8 @@ def _big_queries(arr, n, dev, seed):
 
 
 @pytest.mark.parametrize("name", ["c2_frenet_12x100", "c1_cartesian_1x1000", "dnmpc_4regions_iq",
-                                  "c2b_frenet_1x1000_o10", "cluster_500x10", "dnmpc_9regions_multiv"])
+                                  "c2b_frenet_1x1000_o10", "warmstart_1x500_o10", "cluster_500x10",
+                                  "dnmpc_9regions_multiv"])
 def test_large_batch_equals_piecewise_evaluation_and_oracle(name, cuda_device):
     ops = _ops()
     path = [p for p in golden_paths() if os.path.basename(p)[:-4] == name][0]
