@@ -141,9 +141,14 @@ XLA_FFI_DEFINE_HANDLER_SYMBOL(IrbfnFwdSparse, FwdSparseImpl,
 // VJP of WCRBFNet.apply, tanh gate: (dC, dLS, dW, db, dx).  ws: irbfn_backward_workspace_bytes(B,R,K,D,O,mask).
 static ffi::Error BwdImpl(cudaStream_t s, F32 x, F32 centers, F32 log_sigs, F32 W, F32 lo, F32 hi, S32 off, F32 delta,
                           S32 ranges, F32 dy, RF32 dC, RF32 dLS, RF32 dW, RF32 db, RF32 dx, RU8 ws, int32_t basis,
-                          int32_t grad_mask) {
+                          int32_t grad_mask, float gate_tol) {
   const Dims d = DimsOf(x, centers, (int)W.dimensions()[1]);
   const IrbfnGateDesc g = Gate(lo, hi, off, delta, ranges);
+  if (gate_tol >= 0.0f)   // gate-sparse VJP: terms of (query, region) pairs with gamma <= gate_tol are left out
+    return Check(irbfn_backward_sparse(x.typed_data(), centers.typed_data(), log_sigs.typed_data(), W.typed_data(), nullptr,
+                                       &g, dy.typed_data(), nullptr, dC->typed_data(), dLS->typed_data(), dW->typed_data(),
+                                       db->typed_data(), dx->typed_data(), nullptr, d.B, d.R, d.K, d.D, d.O, basis,
+                                       (unsigned)grad_mask, gate_tol, ws->typed_data(), ws->size_bytes(), s));
   return Check(irbfn_backward(x.typed_data(), centers.typed_data(), log_sigs.typed_data(), W.typed_data(), nullptr, &g,
                               dy.typed_data(), nullptr, dC->typed_data(), dLS->typed_data(), dW->typed_data(),
                               db->typed_data(), dx->typed_data(), nullptr, d.B, d.R, d.K, d.D, d.O, basis,
@@ -155,12 +160,18 @@ XLA_FFI_DEFINE_HANDLER_SYMBOL(IrbfnBwd, BwdImpl,
         .Arg<F32>().Arg<F32>().Arg<S32>().Arg<F32>().Arg<S32>()          // gate constants
         .Arg<F32>()                                                      // dy
         .Ret<F32>().Ret<F32>().Ret<F32>().Ret<F32>().Ret<F32>().Ret<ffi::Buffer<ffi::U8>>()
-        .Attr<int32_t>("basis").Attr<int32_t>("grad_mask"));
+        .Attr<int32_t>("basis").Attr<int32_t>("grad_mask").Attr<float>("gate_tol"));
 
 // Parameter gradients with the gate saved by IrbfnFwdGateOut (training step; no dx): (dC, dLS, dW, db).
 static ffi::Error BwdParamsImpl(cudaStream_t s, F32 x, F32 centers, F32 log_sigs, F32 W, F32 gate, F32 dy, RF32 dC,
-                                RF32 dLS, RF32 dW, RF32 db, RU8 ws, int32_t basis) {
+                                RF32 dLS, RF32 dW, RF32 db, RU8 ws, int32_t basis, float gate_tol) {
   const Dims d = DimsOf(x, centers, (int)W.dimensions()[1]);
+  if (gate_tol >= 0.0f)
+    return Check(irbfn_backward_sparse(x.typed_data(), centers.typed_data(), log_sigs.typed_data(), W.typed_data(),
+                                       gate.typed_data(), nullptr, dy.typed_data(), nullptr, dC->typed_data(),
+                                       dLS->typed_data(), dW->typed_data(), db->typed_data(), nullptr, nullptr, d.B, d.R,
+                                       d.K, d.D, d.O, basis, (unsigned)IRBFN_GRAD_PARAMS, gate_tol, ws->typed_data(),
+                                       ws->size_bytes(), s));
   return Check(irbfn_backward(x.typed_data(), centers.typed_data(), log_sigs.typed_data(), W.typed_data(),
                               gate.typed_data(), nullptr, dy.typed_data(), nullptr, dC->typed_data(), dLS->typed_data(),
                               dW->typed_data(), db->typed_data(), nullptr, nullptr, d.B, d.R, d.K, d.D, d.O, basis,
@@ -169,7 +180,8 @@ static ffi::Error BwdParamsImpl(cudaStream_t s, F32 x, F32 centers, F32 log_sigs
 XLA_FFI_DEFINE_HANDLER_SYMBOL(IrbfnBwdParams, BwdParamsImpl,
     ffi::Ffi::Bind().Ctx<ffi::PlatformStream<cudaStream_t>>()
         .Arg<F32>().Arg<F32>().Arg<F32>().Arg<F32>().Arg<F32>().Arg<F32>()
-        .Ret<F32>().Ret<F32>().Ret<F32>().Ret<F32>().Ret<ffi::Buffer<ffi::U8>>().Attr<int32_t>("basis"));
+        .Ret<F32>().Ret<F32>().Ret<F32>().Ret<F32>().Ret<ffi::Buffer<ffi::U8>>().Attr<int32_t>("basis")
+        .Attr<float>("gate_tol"));
 
 // DeeperWCRBFNet: cotangent of hidden (B,K) -> (dC, dLS, dx).
 static ffi::Error BwdHiddenImpl(cudaStream_t s, F32 x, F32 centers, F32 log_sigs, F32 lo, F32 hi, S32 off, F32 delta,

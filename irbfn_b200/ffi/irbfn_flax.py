@@ -78,8 +78,9 @@ def gate_constants(lower_bounds, upper_bounds, delta, dimension_ranges, activati
 # ------------------------------------------------------------------------------------------------------------------
 # WCRBFNet: y = irbfn_apply(x, centers, log_sigs, W, b)            custom VJP: residuals are x + params (phi recomputed)
 # ------------------------------------------------------------------------------------------------------------------
-@functools.partial(jax.custom_vjp, nondiff_argnums=(5, 6))
-def irbfn_apply(x, centers, log_sigs, W, b, gate_consts, basis):
+@functools.partial(jax.custom_vjp, nondiff_argnums=(5, 6, 7))
+def irbfn_apply(x, centers, log_sigs, W, b, gate_consts, basis, gate_tol=-1.0):
+    # gate_tol >= 0: jax.grad through this call uses the gate-sparse VJP (irbfn_backward_sparse); < 0: dense
     B, D = x.shape
     R, K, _ = centers.shape
     O = W.shape[1]
@@ -90,11 +91,11 @@ def irbfn_apply(x, centers, log_sigs, W, b, gate_consts, basis):
     return y
 
 
-def _apply_fwd(x, centers, log_sigs, W, b, gate_consts, basis):
-    return irbfn_apply(x, centers, log_sigs, W, b, gate_consts, basis), (x, centers, log_sigs, W)
+def _apply_fwd(x, centers, log_sigs, W, b, gate_consts, basis, gate_tol=-1.0):
+    return irbfn_apply(x, centers, log_sigs, W, b, gate_consts, basis, gate_tol), (x, centers, log_sigs, W)
 
 
-def _apply_bwd(gate_consts, basis, res, dy):
+def _apply_bwd(gate_consts, basis, gate_tol, res, dy):
     x, centers, log_sigs, W = res
     B, D = x.shape
     R, K, _ = centers.shape
@@ -104,7 +105,7 @@ def _apply_bwd(gate_consts, basis, res, dy):
             _scratch(_core.irbfn_backward_workspace_bytes(B, R, K, D, O, GRAD_ALL)))
     dC, dLS, dW, db, dx, _ = jax.ffi.ffi_call("IrbfnBwd", outs)(
         _f32(x), _f32(centers), _f32(log_sigs), _f32(W), *gate_consts, _f32(dy),
-        basis=np.int32(basis), grad_mask=np.int32(GRAD_ALL))
+        basis=np.int32(basis), grad_mask=np.int32(GRAD_ALL), gate_tol=np.float32(gate_tol))
     return dx, dC, dLS, dW, db
 
 
@@ -299,6 +300,7 @@ class WCRBFNet(nn.Module):
     centers: Optional[jax.Array] = None
     fixed_centers: Optional[bool] = False
     fixed_width: Optional[bool] = False
+    gate_tol: float = -1.0     # not in the reference: >= 0 selects the gate-sparse VJP (irbfn_backward_sparse)
 
     def setup(self):
         self.num_split_dimensions = len(self.activation_idx)
@@ -311,7 +313,8 @@ class WCRBFNet(nn.Module):
         kernel, bias = self.linear()
         consts = gate_constants(self.lower_bounds, self.upper_bounds, self.delta, self.dimension_ranges,
                                 self.activation_idx)
-        return irbfn_apply(x, centers, log_sigs, kernel, bias, consts, BASIS[self.basis_func.__name__])
+        return irbfn_apply(x, centers, log_sigs, kernel, bias, consts, BASIS[self.basis_func.__name__],
+                           float(self.gate_tol))
 
 
 class DeeperWCRBFNet(nn.Module):
