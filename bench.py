@@ -541,7 +541,10 @@ def extras(net, params, cfg, dev, world, args):
     W_, b_ = p["linear"]["kernel"], p["linear"]["bias"]
     msj = timed(lambda: ops.jacobian(x4, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], W_, gd=gd, basis=0),
                 max(3, args.steps // 2), 3)
-    res["jacobian_8f2"] = {"queries_per_gpu": B4, "ms_one_pass": msj, "ms_jacrev_equivalent": O * ms4,
+    msjs = timed(lambda: ops.jacobian(x4, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], W_, gd=gd, basis=0,
+                                      gate_tol=2.0 ** -24), max(3, args.steps // 2), 3)
+    res["jacobian_8f2"] = {"queries_per_gpu": B4, "ms_one_pass": msj, "ms_one_pass_gate_sparse": msjs,
+                           "ms_jacrev_equivalent": O * ms4,
                            "queries_per_s": world * B4 / (msj * 1e-3),
                            "lane_ops_T_per_s": (R * K * (2 * D + 3 + O * (D + 2))) * B4 / (msj * 1e-3) / 1e12}
     # 8f rank 1: the same C3 step with the reference's Frenet one-step dynamics loss fused in

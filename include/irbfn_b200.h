@@ -400,6 +400,21 @@ int irbfn_jacobian(const float* x, const float* centers, const float* log_sigs, 
                    float* y, float* region_y, int64_t B, int R, int K, int D, int O, int basis,
                    irbfn_stream_t stream);
 
+/*
+ * Gate-sparse one-pass Jacobian (tanh gate): irbfn_jacobian with the terms of every (query, region) pair left out
+ * for which one of the region's interval factors is <= gate_tol (then gamma <= gate_tol, and every term of J and y the
+ * pair contributes carries the factor gamma).  Queries are binned by their set of non-negligible gate intervals
+ * (irbfn_forward_sparse's passes) and a warp skips the regions all of its 64 queries drop -- gate and kernels alike.
+ * No reference call site, like irbfn_jacobian.  Shapes the sparse kernel does not cover (one region,
+ * more than 64 gate intervals, parameters larger than shared memory) run the dense kernel: same result.
+ *   workspace >= irbfn_jacobian_sparse_workspace_bytes(B, gd->num_bounds)
+ */
+size_t irbfn_jacobian_sparse_workspace_bytes(int64_t B, int num_bounds);
+int irbfn_jacobian_sparse(const float* x, const float* centers, const float* log_sigs, const float* W,
+                          const float* bias, const IrbfnGateDesc* gd, float* jac, float* y, int64_t B,
+                          int R, int K, int D, int O, int basis, float gate_tol, void* workspace,
+                          size_t workspace_bytes, irbfn_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Table-side kernels.
  *

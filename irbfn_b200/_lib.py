@@ -34,7 +34,7 @@ EXPORTED_SYMBOLS = (
     "irbfn_forward_gate", "irbfn_forward_streamed", "irbfn_upload_streamed", "irbfn_upload_streamed_available", "irbfn_forward_noalloc", "irbfn_forward_sparse_workspace_bytes", "irbfn_forward_sparse",
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_backward_sparse", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_forward_plan",
-    "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian",
+    "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian", "irbfn_jacobian_sparse_workspace_bytes", "irbfn_jacobian_sparse",
     "irbfn_gather_rows", "irbfn_lattice_queries", "irbfn_grid_index", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
     "irbfn_prediction_loss_workspace_bytes", "irbfn_prediction_loss",
     "irbfn_clip_adam_workspace_bytes", "irbfn_clip_adam",
@@ -132,6 +132,10 @@ def load():
     lib.irbfn_dynamics_loss.argtypes = [i, p, p, p, C.POINTER(C.c_float), p, p, i64, i, i, i64, p, sz, p]
     lib.irbfn_integrate.restype = i
     lib.irbfn_integrate.argtypes = [i, p, C.POINTER(C.c_float), p, i64, i, p]
+    lib.irbfn_jacobian_sparse_workspace_bytes.restype = sz
+    lib.irbfn_jacobian_sparse_workspace_bytes.argtypes = [i64, i]
+    lib.irbfn_jacobian_sparse.restype = i
+    lib.irbfn_jacobian_sparse.argtypes = [p, p, p, p, p, C.POINTER(GateDesc), p, p, i64, i, i, i, i, i, C.c_float, p, sz, p]
     lib.irbfn_jacobian.restype = i
     lib.irbfn_jacobian.argtypes = [p, p, p, p, p, p, C.POINTER(GateDesc), p, p, p, i64, i, i, i, i, i, p]
     lib.irbfn_gather_rows.restype = i

@@ -25,7 +25,8 @@ int launch_bwd_xs_d6(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
 int launch_bwd_xs_d7(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
 int launch_bwd_xs_d8(const BwdXArgs&, int, int, int, size_t, cudaStream_t);
 size_t sparse_bin_workspace_bytes(long long B, int num_bounds);                // irbfn_sparse.cu
-int sparse_bin_queries(const float*, const GateDev&, float, long long, int, int, void*, const int**, cudaStream_t);
+int sparse_bin_queries(const float*, const GateDev&, float, long long, int, int, void*, const int**, cudaStream_t,
+                       const float** edge_out = nullptr);
 int launch_bwd_pw_d4(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_pw_d5(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_bwd_pw_d6(const BwdPWArgs&, int, int, int, int, size_t, cudaStream_t);

@@ -38,13 +38,21 @@ struct JacArgs {
     int RC, KC;             // regions / kernels per stage; RC == R (everything resident) or RC == 1
     int num_tiles;
     int stage_once;
+    // ---- read by the SPARSE instantiations only (irbfn_jacobian_sparse) ----
+    const int* perm;        // (B) queries grouped by their set of non-negligible gate intervals
+    const float* edge;      // (num_bounds, 2): the open interval on which each gate factor exceeds gate_tol
 };
 
 struct JacShape {
     static constexpr int NT = 256, Q = 2, TQ = NT * Q, KT = 4;
 };
 
-template <int D, int OT, int BASIS>
+// SPARSE = 1 (irbfn_jacobian_sparse; tanh gate, resident parameters, at most 64 gate intervals): a (query, region)
+// pair is dropped when one of the region's interval factors is <= gate_tol for the query (then gamma <= gate_tol, and
+// every term of J and y that the pair contributes carries the factor gamma).  The test is a bit mask per query, built
+// once per tile from the interval edges, so a dropped region costs neither its gate nor its kernels; queries are
+// visited in the binned order, so a warp's 64 queries drop the same regions.
+template <int D, int OT, int BASIS, int SPARSE = 0>
 __global__ void __launch_bounds__(JacShape::NT) irbfn_jac_kernel(const JacArgs a) {
     constexpr int NT = JacShape::NT, TQ = JacShape::TQ, KT = JacShape::KT;
     extern __shared__ __align__(16) float smem[];
@@ -62,13 +70,59 @@ __global__ void __launch_bounds__(JacShape::NT) irbfn_jac_kernel(const JacArgs a
     // phi' * 2 exp(-2 ls) from the staged width scale: gaussian row = -s log2e, inverse quadratic row = s
     const float mfac = BASIS == IRBFN_BASIS_GAUSSIAN ? 2.0f / kLog2e : -2.0f;
 
+    // parameters of regions [r_lo, r_lo + nr), kernels [k0, k0 + kc) -> shared memory, transposed per 4-kernel tile
+    auto do_stage = [&](int r_lo, int nr, int k0, int kc, int kcp) {
+        __syncthreads();
+        for (int idx = tid; idx < nr * kcp; idx += NT) {
+            const int sr = idx / kcp, kk = idx - sr * kcp;
+            float* t = stage + ((size_t)sr * KCT + (kk >> 2)) * ((D + 1) * 4) + (kk & 3);
+            if (kk < kc) {
+                const size_t rk = (size_t)(r_lo + sr) * K + (k0 + kk);
+#pragma unroll
+                for (int j = 0; j < D; ++j)
+                    t[4 * j] = j < a.Dsrc ? -__ldg(a.centers + rk * a.Dsrc + j) : 0.f;
+                t[4 * D] = width_scale<BASIS>(__ldg(a.log_sigs + rk));
+            } else {
+#pragma unroll
+                for (int j = 0; j <= D; ++j) t[4 * j] = 0.f;
+            }
+        }
+        for (int idx = tid; idx < kcp * OT; idx += NT) {
+            const int kk = idx / OT, o = idx - kk * OT;
+            Ws[idx] = (kk < kc && o < a.ocur) ? __ldg(a.W + (size_t)(k0 + kk) * a.O + a.o0 + o) : 0.f;
+        }
+        __syncthreads();
+    };
+    if (SPARSE) {
+        // resident parameters are staged BEFORE any warp can skip a region: the staging barriers are CTA-wide
+        do_stage(0, R, 0, K, ((K + KT - 1) / KT) * KT);
+        staged = true;
+    }
+
     for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        const long long qa = (long long)tile * TQ + 2 * tid, qb = qa + 1;
+        long long qa = (long long)tile * TQ + 2 * tid, qb = qa + 1;
+        if (SPARSE) {   // rows in the binned order; a row index >= B means "no query"
+            qa = qa < a.B ? (long long)__ldg(a.perm + qa) : a.B;
+            qb = qb < a.B ? (long long)__ldg(a.perm + qb) : a.B;
+        }
         float2 x2[D];
 #pragma unroll
         for (int j = 0; j < D; ++j) {
             x2[j].x = (qa < a.B && j < a.Dsrc) ? __ldg(a.x + qa * a.Dsrc + j) : 0.f;
             x2[j].y = (qb < a.B && j < a.Dsrc) ? __ldg(a.x + qb * a.Dsrc + j) : 0.f;
+        }
+        unsigned long long sigx = 0ull, sigy = 0ull;   // SPARSE: bit i = interval factor i exceeds gate_tol
+        if (SPARSE) {
+#pragma unroll
+            for (int j = 0; j < D; ++j) {
+                if (j < S) {
+                    for (int i = __ldg(a.gd.offset + j); i < __ldg(a.gd.offset + j + 1); ++i) {
+                        const float lo = __ldg(a.edge + 2 * i), hi = __ldg(a.edge + 2 * i + 1);
+                        if (qa < a.B && x2[j].x > lo && x2[j].x < hi) sigx |= 1ull << i;
+                        if (qb < a.B && x2[j].y > lo && x2[j].y < hi) sigy |= 1ull << i;
+                    }
+                }
+            }
         }
         float2 J[OT][D], y2[OT];
 #pragma unroll
@@ -87,6 +141,14 @@ __global__ void __launch_bounds__(JacShape::NT) irbfn_jac_kernel(const JacArgs a
                 g2.y = qb < a.B ? __ldg(a.gate_ext + qb * R + r) : 0.f;
             } else {
                 if (r >= a.gd.num_ranges) continue;      // gamma == 0 (uniform across the CTA)
+                bool ax = true, ay = true;
+                if (SPARSE) {
+                    unsigned long long req = 0ull;
+                    for (int j = 0; j < S; ++j) req |= 1ull << (__ldg(a.gd.offset + j) + __ldg(a.gd.ranges + r * S + j));
+                    ax = (sigx & req) == req;
+                    ay = (sigy & req) == req;
+                    if (!__any_sync(0xffffffffu, ax || ay)) continue;   // warp-uniform; no barrier inside (resident parameters)
+                }
                 g2 = dup2(1.f);
 #pragma unroll
                 for (int j = 0; j < D; ++j) {
@@ -102,6 +164,10 @@ __global__ void __launch_bounds__(JacShape::NT) irbfn_jac_kernel(const JacArgs a
                         dlg[j * NT + tid] = make_float2(2.f * dl * (sux - slx), 2.f * dl * (suy - sly));
                     }
                 }
+                if (SPARSE) {   // the drop rule is per query: a query's row does not depend on its warp-mates
+                    g2.x = ax ? g2.x : 0.f;
+                    g2.y = ay ? g2.y : 0.f;
+                }
             }
             float2 yr[OT];
 #pragma unroll
@@ -113,27 +179,7 @@ __global__ void __launch_bounds__(JacShape::NT) irbfn_jac_kernel(const JacArgs a
                 const int kc = min(KC, K - k0);
                 const int kcp = ((kc + KT - 1) / KT) * KT;
                 if (!(a.stage_once && staged)) {
-                    __syncthreads();
-                    const int r_lo = a.stage_once ? 0 : r, nr = a.stage_once ? R : 1;
-                    for (int idx = tid; idx < nr * kcp; idx += NT) {
-                        const int sr = idx / kcp, kk = idx - sr * kcp;
-                        float* t = stage + ((size_t)sr * KCT + (kk >> 2)) * ((D + 1) * 4) + (kk & 3);
-                        if (kk < kc) {
-                            const size_t rk = (size_t)(r_lo + sr) * K + (k0 + kk);
-#pragma unroll
-                            for (int j = 0; j < D; ++j)
-                                t[4 * j] = j < a.Dsrc ? -__ldg(a.centers + rk * a.Dsrc + j) : 0.f;
-                            t[4 * D] = width_scale<BASIS>(__ldg(a.log_sigs + rk));
-                        } else {
-#pragma unroll
-                            for (int j = 0; j <= D; ++j) t[4 * j] = 0.f;
-                        }
-                    }
-                    for (int idx = tid; idx < kcp * OT; idx += NT) {
-                        const int kk = idx / OT, o = idx - kk * OT;
-                        Ws[idx] = (kk < kc && o < a.ocur) ? __ldg(a.W + (size_t)(k0 + kk) * a.O + a.o0 + o) : 0.f;
-                    }
-                    __syncthreads();
+                    do_stage(a.stage_once ? 0 : r, a.stage_once ? R : 1, k0, kc, kcp);
                     staged = true;
                 }
 

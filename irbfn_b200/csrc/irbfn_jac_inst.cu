@@ -10,9 +10,9 @@
 
 namespace irbfn {
 namespace {
-template <int OT, int BASIS>
+template <int OT, int BASIS, int SPARSE = 0>
 int launch_inst(const JacArgs& a, int sms, size_t smem, int* grid_out, cudaStream_t st) {
-    auto kern = irbfn_jac_kernel<IRBFN_D, OT, BASIS>;
+    auto kern = irbfn_jac_kernel<IRBFN_D, OT, BASIS, SPARSE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     int per_sm = 1;
@@ -33,5 +33,14 @@ int IRBFN_CAT(launch_jac_d, IRBFN_D)(const JacArgs& a, int OT, int basis, int sm
                        : launch_inst<4, IRBFN_BASIS_GAUSSIAN>(a, sms, smem, nullptr, st);
     return OT == 2 ? launch_inst<2, IRBFN_BASIS_INVERSE_QUADRATIC>(a, sms, smem, nullptr, st)
                    : launch_inst<4, IRBFN_BASIS_INVERSE_QUADRATIC>(a, sms, smem, nullptr, st);
+}
+
+// gate-sparse instantiations (irbfn_jacobian_sparse)
+int IRBFN_CAT(launch_jacs_d, IRBFN_D)(const JacArgs& a, int OT, int basis, int sms, size_t smem, cudaStream_t st) {
+    if (basis == IRBFN_BASIS_GAUSSIAN)
+        return OT == 2 ? launch_inst<2, IRBFN_BASIS_GAUSSIAN, 1>(a, sms, smem, nullptr, st)
+                       : launch_inst<4, IRBFN_BASIS_GAUSSIAN, 1>(a, sms, smem, nullptr, st);
+    return OT == 2 ? launch_inst<2, IRBFN_BASIS_INVERSE_QUADRATIC, 1>(a, sms, smem, nullptr, st)
+                   : launch_inst<4, IRBFN_BASIS_INVERSE_QUADRATIC, 1>(a, sms, smem, nullptr, st);
 }
 }  // namespace irbfn

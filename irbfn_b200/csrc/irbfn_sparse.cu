@@ -262,7 +262,7 @@ __global__ void set_thr_kernel(float* thr, float v) { *thr = v; }
 size_t sparse_bin_workspace_bytes(long long B, int num_bounds) { return sparse_layout(B, num_bounds).total; }
 
 int sparse_bin_queries(const float* x, const GateDev& gdev, float thr_value, long long B, int D, int sms, void* workspace,
-                       const int** perm_out, cudaStream_t st) {
+                       const int** perm_out, cudaStream_t st, const float** edge_out) {
     const SparseLayout L = sparse_layout(B, gdev.num_bounds);
     char* ws = (char*)workspace;
     float* thr = (float*)(ws + L.thr_off);
@@ -290,6 +290,7 @@ int sparse_bin_queries(const float* x, const GateDev& gdev, float thr_value, lon
         sparse_scatter_kernel<<<nblk, 256, 0, st>>>(keys, hist, perm, B);
     }
     *perm_out = perm;
+    if (edge_out != nullptr) *edge_out = edge;
     return (int)cudaGetLastError();
 }
 

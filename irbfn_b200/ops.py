@@ -502,9 +502,11 @@ def integrate(model: int, x_and_u, dyn_params):
 
 # --------------------------------------------------------------------------- one-pass Jacobian
 def jacobian(x, centers, log_sigs, kernel, bias=None, *, gate=None, gd: GatePack = None,
-             basis: int = BASIS_GAUSSIAN, want_y: bool = False, want_region_y: bool = False):
+             basis: int = BASIS_GAUSSIAN, want_y: bool = False, want_region_y: bool = False,
+             gate_tol: Optional[float] = None):
     """dy/dx (B,O,D) of the IRBFN forward in one launch per 4 output columns (irbfn_jacobian).
-    Returns jac, or (jac, y) / (jac, y, region_y) when asked."""
+    Returns jac, or (jac, y) / (jac, y, region_y) when asked.  ``gate_tol`` (>= 0, tanh gate): the gate-sparse kernel
+    (irbfn_jacobian_sparse) -- (query, region) pairs with an interval factor <= gate_tol are left out."""
     lib = _lib.load()
     _chk(x, "x")
     B, D = x.shape
@@ -527,7 +529,17 @@ def jacobian(x, centers, log_sigs, kernel, bias=None, *, gate=None, gd: GatePack
     ry = torch.empty((B, R, O), device=x.device, dtype=torch.float32) if want_region_y else None
     if want_region_y and gate is None and gd is not None and gd.num_ranges < R:
         ry.zero_()          # regions without a range row have gamma == 0 and are skipped
-    if B > 0:
+    if B > 0 and gate_tol is not None:
+        if gd is None or want_region_y:
+            raise ValueError("gate_tol needs the tanh gate (gd) and no region_y")
+        with torch.cuda.device(x.device):
+            nbytes = lib.irbfn_jacobian_sparse_workspace_bytes(B, gd.desc.num_bounds)
+            ws = _workspace(nbytes, x.device)
+            rc = lib.irbfn_jacobian_sparse(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel),
+                                           _ptr(bias) if want_y else None, gd.ref(), _ptr(jac), _ptr(y), B, R, K, D, O,
+                                           basis, float(gate_tol), _ptr(ws), nbytes, _stream())
+        _lib.check(rc, "irbfn_jacobian_sparse")
+    elif B > 0:
         with torch.cuda.device(x.device):
             rc = lib.irbfn_jacobian(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias) if want_y else None,
                                     _ptr(gate), gd.ref() if gd is not None else None, _ptr(jac), _ptr(y),

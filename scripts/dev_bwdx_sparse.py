@@ -38,3 +38,13 @@ for tol in (0.0, 2.0 ** -24, 1e-6):
     t = timed(lambda: ops.backward(x, c, ls, W, dy, gd=gd, basis=0, grad_mask=ops.GRAD_X, gate_tol=tol))
     print("  gate_tol %-8.2g %8.1f us (%.2fx)  rel-L2 vs dense %.2e  max|d|/max|dx| %.2e"
           % (tol, t, t0 / t, float((g - dense).norm() / dense.norm()), float((g - dense).abs().max() / dense.abs().max())))
+
+# one-pass Jacobian on the same queries
+jd = ops.jacobian(x, c, ls, W, gd=gd, basis=0)
+tj = timed(lambda: ops.jacobian(x, c, ls, W, gd=gd, basis=0), n=10)
+print("C4 Jacobian dense %8.1f us" % tj)
+for tol in (0.0, 2.0 ** -24, 1e-6):
+    js = ops.jacobian(x, c, ls, W, gd=gd, basis=0, gate_tol=tol)
+    t = timed(lambda: ops.jacobian(x, c, ls, W, gd=gd, basis=0, gate_tol=tol), n=10)
+    print("  gate_tol %-8.2g %8.1f us (%.2fx)  rel-L2 vs dense %.2e  max|d|/max|J| %.2e"
+          % (tol, t, tj / t, float((js - jd).norm() / jd.norm()), float((js - jd).abs().max() / jd.abs().max())))

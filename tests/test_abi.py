@@ -93,8 +93,10 @@ def test_backward_argument_validation():
     assert bwd(_lib.GRAD_PARAMS, D=9) == -2
     assert bwd(_lib.GRAD_PARAMS, B=0) == 0
     assert lib.irbfn_backward_workspace_bytes(1 << 18, 12, 100, 8, 2, _lib.GRAD_PARAMS) > 0
-    # dx alone needs only the (B,R) scratch for d gamma of the tanh gate
-    assert lib.irbfn_backward_workspace_bytes(1 << 18, 12, 100, 8, 2, _lib.GRAD_X) == (1 << 18) * 12 * 4
+    # dx alone needs the (B,R) scratch for d gamma of the tanh gate plus the binning scratch of the gate-sparse pass
+    # (irbfn_backward_sparse: 8 bytes per query, a histogram and the interval edges -- under 7 MB here)
+    n = lib.irbfn_backward_workspace_bytes(1 << 18, 12, 100, 8, 2, _lib.GRAD_X)
+    assert (1 << 18) * (12 * 4 + 8) <= n <= (1 << 18) * (12 * 4 + 8) + (5 << 20)
 
 
 def test_no_cpu_fallback_when_library_missing(monkeypatch, tmp_path):

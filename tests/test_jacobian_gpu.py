@@ -112,3 +112,51 @@ def test_jacobian_finite_on_centre_and_errors(cuda_device):
         ops.jacobian(_t(x, d), _t(p["centers"], d), _t(p["log_sigs"], d), _t(p["kernel"], d))     # no gate at all
     assert ops.jacobian(_t(x[:0], d), _t(p["centers"], d), _t(p["log_sigs"], d), _t(p["kernel"], d),
                         gd=_gd(cfg, d)).shape == (0, 2, 4)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Gate-sparse Jacobian (irbfn_jacobian_sparse): (query, region) pairs with an interval factor <= gate_tol are left out.
+# ---------------------------------------------------------------------------------------------------
+GATE_TOL = 2.0 ** -24
+
+
+@pytest.mark.parametrize("name", WCRBF)
+def test_sparse_jacobian_matches_oracle_on_shipped_parameters(name, cuda_device):
+    ops = _ops()
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, name + ".npz"))
+    n = 512
+    x = arr["x"][:n]
+    J_ref = orc.wcrbf_jacobian(x.astype(np.float64), params, cfg)
+    rb, lin = params["rbf_list"], params["linear"]
+    args = (_t(x, cuda_device), _t(rb["centers"], cuda_device), _t(rb["log_sigs"], cuda_device),
+            _t(lin["kernel"], cuda_device), _t(lin["bias"], cuda_device))
+    kw = dict(gd=_gd(cfg, cuda_device), basis=orc.BASIS_IDS[cfg["basis_func"]], want_y=True)
+    jac, y = ops.jacobian(*args, gate_tol=GATE_TOL, **kw)
+    assert rel_l2(jac.cpu().numpy(), J_ref) <= 1e-4
+    assert rel_max(y.cpu().numpy(), arr["y64"][:n]) <= 1e-5
+    jac2, y2 = ops.jacobian(*args, gate_tol=GATE_TOL, **kw)
+    assert torch.equal(jac, jac2) and torch.equal(y, y2)   # the binning order cannot change a query's rows
+
+
+@pytest.mark.parametrize("shape", [(5000, 12, 100, 8, 2, 3), (3001, 27, 30, 8, 10, 3), (2049, 64, 16, 6, 5, 3),
+                                   (777, 5, 33, 5, 4, 2)], ids=lambda s: "B%d_R%d_K%d_D%d_O%d_S%d" % s)
+@pytest.mark.parametrize("basis", [0, 1])
+def test_sparse_jacobian_with_sharp_gates(shape, basis, cuda_device):
+    """Uniform queries, sharp gates: most (query, region) pairs are skipped; against the dense float64 jacrev."""
+    ops = _ops()
+    B, R, K, D, O, S = shape
+    cfg, p, x = _synthetic(47, B, R, K, D, O, S=S, nb=(4, 3, 2))
+    cfg["delta"] = [40.0] * len(cfg["delta"])
+    cfg["basis_func"] = "gaussian" if basis == 0 else "inverse_quadratic"
+    tree = {"rbf_list": {"centers": p["centers"], "log_sigs": p["log_sigs"]},
+            "linear": {"kernel": p["kernel"], "bias": p["bias"]}}
+    idx = np.arange(0, B, 7)
+    J_ref = orc.wcrbf_jacobian(x[idx].astype(np.float64), tree, cfg)
+    d = cuda_device
+    jac, y = ops.jacobian(_t(x, d), _t(p["centers"], d), _t(p["log_sigs"], d), _t(p["kernel"], d), _t(p["bias"], d),
+                          gd=_gd(cfg, d), basis=basis, want_y=True, gate_tol=GATE_TOL)
+    assert rel_l2(jac[torch.tensor(idx, device=d)].cpu().numpy(), J_ref) <= 1e-4
+    y_ref = orc.wcrbf_forward(x[idx].astype(np.float64), tree, cfg)
+    assert rel_max(y[torch.tensor(idx, device=d)].cpu().numpy(), y_ref) <= 1e-5
+    dense = ops.jacobian(_t(x, d), _t(p["centers"], d), _t(p["log_sigs"], d), _t(p["kernel"], d), gd=_gd(cfg, d), basis=basis)
+    assert rel_l2(jac.cpu().numpy(), dense.cpu().numpy().astype(np.float64)) <= 1e-5
