@@ -346,7 +346,7 @@ def main():
             # ... and one flat summary of them at the very end (a 1,500-character tail of the line always holds it)
             r4 = lambda v: None if v is None else float("%.4g" % v)
             c3, o10, c1s, c4, c5, dp = (tail.get(k) or {} for k in ("c3", "c3_o10_fullint", "c3_c1shape", "c4", "c5", "dp_parity"))
-            sp = lambda d: (d.get("gate_sparse_vjp") or {}).get("ms_graph")
+            sp = lambda d: (d.get("gate_sparse_step") or {}).get("ms_graph")
             out["summary"] = {
                 "n_gpus": world, "fwd_ms": r4(ms), "e2e_ms": r4(ms_e2e),
                 "c3_ms_graph": r4(c3.get("ms_graph")), "c3_ms_graph_nccl": r4(c3.get("ms_graph_nccl")),
@@ -444,9 +444,12 @@ def extras(net, params, cfg, dev, world, args):
         gstep_n = GraphedTrainStep(st_n, x.shape[0], GB, loss="l2").load(x, y)
         ms_graph_nccl = timed(lambda: gstep_n(), args.steps, args.warmup)
         del gstep_n, st_n
-    # the same step with gate-sparse parameter gradients (irbfn_backward_sparse, gate_tol = 2^-24): the backward
-    # skips the (sample, region) pairs whose gate cannot move a gradient; the forward stays dense
+    # the same step gate-sparse (gate_tol = 2^-24): forward (irbfn_forward_sparse_gate: binned samples, regions skipped
+    # per warp) and parameter gradients (irbfn_backward_sparse: a ballot per 32 samples) leave out the (sample, region)
+    # pairs whose gate cannot move an output or a gradient
     GATE_TOL = 2.0 ** -24
+    # (the forward stays dense here: on uniformly drawn samples at 12 regions its gate-sparse variant gains less than
+    # its binning pass and the backward's own gate pass cost -- 0.527 against 0.514 ms; it pays at 27 regions, below)
     st_s = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev, gate_tol=GATE_TOL)
     st_s.enable_peer_allreduce()
     ms_t_sp = timed(lambda: train_step(st_s, x, y, GB), args.steps, args.warmup)
@@ -477,7 +480,8 @@ def extras(net, params, cfg, dev, world, args):
                   "ms_kernels_this_rank": ms_local, "ms_nccl_allreduce_alone": ms_ar,
                   "ms_fwd_vjp_allreduce": ms_g, "allreduce_bytes": int(state._grad_ext.numel() * 4),
                   "lane_ops_T_per_s": lane_step * GB / (min(ms_t, ms_graph) * 1e-3) / 1e12,
-                  "gate_sparse_vjp": {"gate_tol": GATE_TOL, "ms_eager": ms_t_sp, "ms_graph": ms_graph_sp,
+                  "gate_sparse_step": {"gate_tol": GATE_TOL, "forward": "dense", "ms_eager": ms_t_sp,
+                                       "ms_graph": ms_graph_sp,
                                       "grad_rel_l2_vs_dense_max_over_leaves": sp_dev}}
 
     # 8(e) result check on hardware: the NCCL-reduced gradient of the sharded step against the gradient of
@@ -621,19 +625,24 @@ def train_case(fixture, loss, GB, dev, rank, world, args, timed):
     lane = R * K * (2 * D + 2) + K * O + R * K * (3 * D + 5) + 2 * K * O
     sparse = None
     if R > 1:   # gate-sparse parameter gradients (irbfn_backward_sparse), as in c3
-        st_s = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev, gate_tol=2.0 ** -24)
+        yscale = float(net.apply(params, x).abs().max())
+        st_s = TrainState(net, params, lr=1e-3, max_grad_norm=1.0, device=dev, gate_tol=2.0 ** -24,
+                          fwd_tol_abs=1e-6 * yscale)
         st_s.enable_peer_allreduce()
         gstep_s = GraphedTrainStep(st_s, x.shape[0], GB, loss=loss).load(x, y)
         ms_graph_sp = timed(lambda: gstep_s(), steps, 3)
         st_s.flat.copy_(state.flat)
-        grad_step(st_s, x, y, GB, loss)
-        grad_step(state, x, y, GB, loss)
+        # deviation of the gradients under the SMOOTH l2 loss: the full-integration loss clips (dynamics.py), and a 1e-6
+        # change of y_pred -- fp32 rounding of any two correct forwards -- flips a clip for a few samples
+        grad_step(st_s, x, y, GB, "l2")
+        grad_step(state, x, y, GB, "l2")
         dev_sp = max(float((st_s.gviews[k].double() - state.gviews[k].double()).norm() / state.gviews[k].double().norm())
                      for k in state.gviews)
-        sparse = {"gate_tol": 2.0 ** -24, "ms_graph": ms_graph_sp, "grad_rel_l2_vs_dense_max_over_leaves": dev_sp}
+        sparse = {"gate_tol": 2.0 ** -24, "forward": "gate-sparse, tol_abs = 1e-6 max|y|", "ms_graph": ms_graph_sp,
+                  "grad_rel_l2_vs_dense_max_over_leaves_l2_loss": dev_sp}
         del gstep_s, st_s
     return {"shape": "R%d_K%d_D%d_O%d" % (R, K, D, O), "loss": loss, "global_batch": GB, "n_gpus": world,
-            "ms_eager": ms_t, "ms_graph": ms_graph, "ms_fwd_loss_vjp_allreduce": ms_g, "gate_sparse_vjp": sparse,
+            "ms_eager": ms_t, "ms_graph": ms_graph, "ms_fwd_loss_vjp_allreduce": ms_g, "gate_sparse_step": sparse,
             "lane_ops_T_per_s": lane * GB / (ms_g * 1e-3) / 1e12,
             "allreduce_bytes": int(state._grad_ext.numel() * 4), "allreduce": how}
 

@@ -208,6 +208,12 @@ int irbfn_forward_sparse(const float* x, const float* centers, const float* log_
                          const float* bias, const IrbfnGateDesc* gd, float* y, int64_t B, int R, int K,
                          int D, int O, int basis, float tol_abs, uint64_t* counters, void* workspace,
                          size_t workspace_bytes, irbfn_stream_t stream);
+/* The same with the GATE threshold given directly (a local network is skipped for a query when gamma_r <= gate_tol):
+ * the forward of a gate-sparse training step, which hands the same threshold to irbfn_backward_sparse. */
+int irbfn_forward_sparse_gate(const float* x, const float* centers, const float* log_sigs, const float* W,
+                              const float* bias, const IrbfnGateDesc* gd, float* y, int64_t B, int R, int K,
+                              int D, int O, int basis, float gate_tol, uint64_t* counters, void* workspace,
+                              size_t workspace_bytes, irbfn_stream_t stream);
 
 /*
  * Backward (VJP).  Recomputes phi from x and the parameters; nothing from the forward is saved.

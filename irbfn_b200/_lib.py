@@ -31,7 +31,7 @@ DYN_FRENET_MULT, DYN_FRENET_ONESTEP_AUX, DYN_ST_MULT, DYN_ST_ONESTEP_AUX = 0, 1,
 # every symbol include/irbfn_b200.h declares (tests check the .so exports exactly these)
 EXPORTED_SYMBOLS = (
     "irbfn_abi_version", "irbfn_error_string", "irbfn_last_error_detail", "irbfn_forward_workspace_bytes", "irbfn_forward",
-    "irbfn_forward_gate", "irbfn_forward_streamed", "irbfn_upload_streamed", "irbfn_upload_streamed_available", "irbfn_forward_noalloc", "irbfn_forward_sparse_workspace_bytes", "irbfn_forward_sparse",
+    "irbfn_forward_gate", "irbfn_forward_streamed", "irbfn_upload_streamed", "irbfn_upload_streamed_available", "irbfn_forward_noalloc", "irbfn_forward_sparse_workspace_bytes", "irbfn_forward_sparse", "irbfn_forward_sparse_gate",
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_backward_sparse", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_forward_plan",
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian", "irbfn_jacobian_sparse_workspace_bytes", "irbfn_jacobian_sparse",
@@ -96,6 +96,8 @@ def load():
     lib.irbfn_forward_sparse_workspace_bytes.argtypes = [i64, i]
     lib.irbfn_forward_sparse.restype = i
     lib.irbfn_forward_sparse.argtypes = [p, p, p, p, p, C.POINTER(GateDesc), p, i64, i, i, i, i, i, C.c_float, p, p, sz, p]
+    lib.irbfn_forward_sparse_gate.restype = i
+    lib.irbfn_forward_sparse_gate.argtypes = lib.irbfn_forward_sparse.argtypes
     lib.irbfn_backward_workspace_bytes.restype = sz
     lib.irbfn_backward_workspace_bytes.argtypes = [i64, i, i, i, i, u]
     lib.irbfn_backward.restype = i

@@ -303,10 +303,34 @@ extern "C" size_t irbfn_forward_sparse_workspace_bytes(int64_t B, int num_bounds
     return sparse_layout(B, num_bounds).total;
 }
 
+// tol_is_gate = 0: tol is the absolute output tolerance, the gate threshold is derived from W (wabs_thr_kernel).
+// tol_is_gate = 1: tol IS the gate threshold (irbfn_forward_sparse_gate: the training step, which hands the same
+// threshold to irbfn_backward_sparse).
+static int forward_sparse_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
+                               const float* bias, const IrbfnGateDesc* gd, float* y, int64_t B, int R, int K,
+                               int D, int O, int basis, float tol_abs, int tol_is_gate, uint64_t* counters,
+                               void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
+
 extern "C" int irbfn_forward_sparse(const float* x, const float* centers, const float* log_sigs, const float* W,
                                     const float* bias, const IrbfnGateDesc* gd, float* y, int64_t B, int R, int K,
                                     int D, int O, int basis, float tol_abs, uint64_t* counters, void* workspace,
                                     size_t workspace_bytes, irbfn_stream_t stream) {
+    return forward_sparse_impl(x, centers, log_sigs, W, bias, gd, y, B, R, K, D, O, basis, tol_abs, 0, counters,
+                               workspace, workspace_bytes, stream);
+}
+
+extern "C" int irbfn_forward_sparse_gate(const float* x, const float* centers, const float* log_sigs, const float* W,
+                                         const float* bias, const IrbfnGateDesc* gd, float* y, int64_t B, int R,
+                                         int K, int D, int O, int basis, float gate_tol, uint64_t* counters,
+                                         void* workspace, size_t workspace_bytes, irbfn_stream_t stream) {
+    return forward_sparse_impl(x, centers, log_sigs, W, bias, gd, y, B, R, K, D, O, basis, gate_tol, 1, counters,
+                               workspace, workspace_bytes, stream);
+}
+
+static int forward_sparse_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
+                               const float* bias, const IrbfnGateDesc* gd, float* y, int64_t B, int R, int K,
+                               int D, int O, int basis, float tol_abs, int tol_is_gate, uint64_t* counters,
+                               void* workspace, size_t workspace_bytes, irbfn_stream_t stream) {
     if (B < 0 || R <= 0 || K <= 0 || D <= 0 || O <= 0) return IRBFN_ERR_BAD_DIMS;
     if (B > 0x7fffffffll) return IRBFN_ERR_BAD_DIMS;                   // perm holds int32 row numbers
     if (D > IRBFN_MAX_D) return IRBFN_ERR_UNSUPPORTED_D;
@@ -334,7 +358,8 @@ extern "C" int irbfn_forward_sparse(const float* x, const float* centers, const 
 
     if (cudaMemsetAsync(ws + L.skip_off, 0, L.keys_off - L.skip_off, st) != cudaSuccess)      // counters + histogram
         return note_cuda_error("cudaMemsetAsync", (int)cudaGetLastError());
-    wabs_thr_kernel<<<1, 256, 0, st>>>(W, K, O, R, tol_abs, thr);
+    if (tol_is_gate) set_thr_kernel<<<1, 1, 0, st>>>(thr, tol_abs);
+    else wabs_thr_kernel<<<1, 256, 0, st>>>(W, K, O, R, tol_abs, thr);
     const int nblk = (int)((B + 255) / 256 < (long long)sms * 16 ? (B + 255) / 256 : (long long)sms * 16);
     float* edge = (float*)(ws + L.edge_off);
     sparse_edges_kernel<<<1, 64, 0, st>>>(gdev, thr, edge);

@@ -145,10 +145,11 @@ def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: Gate
 
 
 def forward_sparse(x, centers, log_sigs, kernel, bias, *, gd: GatePack, basis: int = BASIS_GAUSSIAN,
-                   tol_abs: float = 0.0, out=None, counters=None):
+                   tol_abs: float = 0.0, out=None, counters=None, gate_tol: Optional[float] = None):
     """Gate-sparse, region-binned forward (irbfn_forward_sparse): y within ``tol_abs`` (absolute, per output) of
     ``forward``.  ``counters``: optional int64 CUDA tensor of 2 elements receiving the number of (warp, region)
-    evaluations skipped / done."""
+    evaluations skipped / done.  ``gate_tol`` instead of ``tol_abs``: the gate threshold itself
+    (irbfn_forward_sparse_gate: a local network is skipped for a query when its gate is <= gate_tol)."""
     lib = _lib.load()
     _chk(x, "x")
     B, D = x.shape
@@ -171,9 +172,9 @@ def forward_sparse(x, centers, log_sigs, kernel, bias, *, gd: GatePack, basis: i
     with torch.cuda.device(x.device):
         nbytes = lib.irbfn_forward_sparse_workspace_bytes(B, gd.desc.num_bounds)
         ws = _workspace(nbytes, x.device)
-        rc = lib.irbfn_forward_sparse(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias), gd.ref(),
-                                      _ptr(y), B, R, K, D, O, basis, float(tol_abs), _ptr(counters), _ptr(ws), nbytes,
-                                      _stream())
+        fn = lib.irbfn_forward_sparse if gate_tol is None else lib.irbfn_forward_sparse_gate
+        rc = fn(_ptr(x), _ptr(centers), _ptr(log_sigs), _ptr(kernel), _ptr(bias), gd.ref(), _ptr(y), B, R, K, D, O, basis,
+                float(tol_abs if gate_tol is None else gate_tol), _ptr(counters), _ptr(ws), nbytes, _stream())
     _lib.check(rc, "irbfn_forward_sparse")
     return y
 

@@ -30,7 +30,7 @@ class TrainState:
 
     def __init__(self, module: WCRBFNet, params: dict, lr: float, max_grad_norm: float = 1.0,
                  b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, device=None,
-                 gate_tol: Optional[float] = None):
+                 gate_tol: Optional[float] = None, fwd_tol_abs: Optional[float] = None):
         if not isinstance(module, WCRBFNet):
             raise TypeError("TrainState drives WCRBFNet (the shape train_nmpc*.py trains)")
         p = _unwrap(params)
@@ -84,6 +84,12 @@ class TrainState:
         # None: dense parameter gradients.  >= 0: gate-sparse (irbfn_backward_sparse): the terms of (sample, region)
         # pairs whose gate is <= gate_tol are left out of the parameter gradients (2^-24 changes them by ~4e-8)
         self.gate_tol = gate_tol
+        # fwd_tol_abs (>= 0): the step's FORWARD is gate-sparse too (irbfn_forward_sparse: every output within
+        # fwd_tol_abs of the dense forward -- an ABSOLUTE output tolerance, because the threshold on the gate that keeps
+        # the outputs accurate depends on the size of the readout weights); the backward then takes the gate description
+        # instead of the gate the dense forward would have written
+        self.fwd_tol_abs = fwd_tol_abs
+        self.sparse_forward = fwd_tol_abs is not None and module.num_regions > 1
         self.fused_tail = n + 1 <= ops.fused_update_max_n() if device.type == "cuda" else False
 
     def enable_peer_allreduce(self) -> str:
@@ -246,7 +252,15 @@ def _local_grad(state: TrainState, x: torch.Tensor, y: torch.Tensor, gb: int, lo
     B = int(x.shape[0])
     if state.gate_buf is None or state.gate_buf.shape[0] != B:
         state.gate_buf = torch.empty((B, m.num_regions), device=dev, dtype=torch.float32)
-    y_pred = ops.forward(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis, gate_out=state.gate_buf)
+    sparse_fwd = state.sparse_forward and B < (1 << 31)
+    if sparse_fwd:
+        y_pred = ops.forward_sparse(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis,
+                                    tol_abs=state.fwd_tol_abs)
+        gate_kw = dict(gd=gd)
+    else:
+        y_pred = ops.forward(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis,
+                             gate_out=state.gate_buf)
+        gate_kw = dict(gate=state.gate_buf)
     if loss in DYNAMICS_LOSSES:
         terms, dy = ops.dynamics_loss(DYNAMICS_LOSSES[loss], x, y_pred, y, state.dyn_params, gb)
         state.loss_terms = terms          # [pred_loss, int_loss] of this shard (device)
@@ -256,12 +270,12 @@ def _local_grad(state: TrainState, x: torch.Tensor, y: torch.Tensor, gb: int, lo
         # buffer the collective reduces: it rides along, still one collective, no concat, no copy
         n = state.grad.numel()
         lv, dy = ops.prediction_loss(y_pred, y, gb, loss, loss=state._grad_src[n:n + 1])
-        ops.backward(x, centers, log_sigs, v["kernel"], dy, gate=state.gate_buf, basis=m._basis,
-                     grad_mask=state.mask, flat_out=state._grad_src[:n], gate_tol=state.gate_tol)
+        ops.backward(x, centers, log_sigs, v["kernel"], dy, basis=m._basis, grad_mask=state.mask,
+                     flat_out=state._grad_src[:n], gate_tol=state.gate_tol, **gate_kw)
         return lv[0]
     n = state.grad.numel()
-    ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), gate=state.gate_buf, basis=m._basis,
-                 grad_mask=state.mask, flat_out=state._grad_src[:n], gate_tol=state.gate_tol)
+    ops.backward(x, centers, log_sigs, v["kernel"], dy.contiguous(), basis=m._basis, grad_mask=state.mask,
+                 flat_out=state._grad_src[:n], gate_tol=state.gate_tol, **gate_kw)
     state._grad_src[n:n + 1].copy_(lval.reshape(1))      # the loss rides along: still one collective, no concat
     return lval
 

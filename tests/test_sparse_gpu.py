@@ -215,3 +215,34 @@ def test_module_autograd_uses_the_sparse_vjp_when_gate_tol_is_set(cuda_device):
     again = grads()
     for a, b in zip(again, dense):
         assert torch.equal(a, b)                      # switching it off restores the dense VJP
+
+
+def test_gate_sparse_training_step_matches_the_dense_step(cuda_device):
+    """TrainState(gate_tol=..., fwd_tol_abs=...): gate-sparse VJP (and forward) inside the data-parallel step; the
+    flat gradient and the loss agree with the dense step, and an optimiser step moves the parameters alike."""
+    from conftest import GOLDEN_DIR
+    from irbfn_b200.basis import gaussian
+    from irbfn_b200.model import WCRBFNet, device_params
+    from irbfn_b200.train import TrainState, grad_step, train_step
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                   cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"], cfg["delta"])
+    dp = device_params({"params": params}, cuda_device)
+    lo = np.array([min(b) for b in cfg["lower_bounds"]], np.float32)
+    hi = np.array([max(b) for b in cfg["upper_bounds"]], np.float32)
+    g = torch.Generator().manual_seed(3)
+    x = (torch.rand((20000, 8), generator=g) * torch.from_numpy(hi - lo) + torch.from_numpy(lo)).to(cuda_device)
+    y = torch.randn((20000, 2), generator=g).to(cuda_device)
+    dense = TrainState(net, dp, lr=1e-3, device=cuda_device)
+    yscale = float(net.apply(dp, x).abs().max())
+    for kw in (dict(gate_tol=GATE_TOL), dict(gate_tol=GATE_TOL, fwd_tol_abs=1e-6 * yscale)):
+        sparse = TrainState(net, dp, lr=1e-3, device=cuda_device, **kw)
+        l0 = grad_step(dense, x, y)
+        l1 = grad_step(sparse, x, y)
+        assert abs(float(l0) - float(l1)) <= 1e-5 * abs(float(l0))
+        for k in dense.gviews:
+            assert _rel_l2(sparse.gviews[k].cpu().numpy(), dense.gviews[k].cpu().numpy()) < 1e-5, (kw, k)
+        train_step(sparse, x, y)
+        d2 = TrainState(net, dp, lr=1e-3, device=cuda_device)
+        train_step(d2, x, y)
+        assert _rel_l2(sparse.flat.cpu().numpy(), d2.flat.cpu().numpy()) < 1e-6
