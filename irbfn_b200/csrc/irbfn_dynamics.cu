@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(kLossThreads) dynamics_loss_kernel(const LossA
 // Sum of the per-block (prediction, integration) loss partials: thread t adds blocks t, t+256, ... in
 // order, then a fixed shared-memory tree; one block, deterministic.
 __global__ void __launch_bounds__(256) dynamics_loss_reduce_kernel(const double* part, int nblocks, double sp,
-                                                                   double si, float* losses) {
+                                                                   double si, float* losses, int nout) {
     __shared__ double rp[256], ri[256];
     const int t = threadIdx.x;
     double tp = 0.0, ti = 0.0;
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(256) dynamics_loss_reduce_kernel(const double*
     }
     if (t == 0) {
         losses[0] = (float)(rp[0] * sp);
-        losses[1] = (float)(ri[0] * si);
+        if (nout > 1) losses[1] = (float)(ri[0] * si);   // the prediction-only loss has ONE output word
     }
 }
 
@@ -365,7 +365,7 @@ extern "C" int irbfn_dynamics_loss(int mode, const float* x, const float* y_pred
     else if (mode == IRBFN_LOSS_ST_ONEINT) e = O == 2 ? launch_loss<2, 2>(a, blocks, st) : launch_loss<2, 10>(a, blocks, st);
     else e = launch_loss<3, 10>(a, blocks, st);
     if (e != 0) return note_cuda_error("dynamics_loss_kernel", e);
-    dynamics_loss_reduce_kernel<<<1, 256, 0, st>>>((const double*)workspace, blocks, sp, si, losses);
+    dynamics_loss_reduce_kernel<<<1, 256, 0, st>>>((const double*)workspace, blocks, sp, si, losses, 2);
     e = (int)cudaGetLastError();
     if (e != 0) return note_cuda_error("dynamics_loss_reduce_kernel", e);
     return IRBFN_OK;
@@ -392,7 +392,7 @@ extern "C" int irbfn_prediction_loss(int kind, const float* y_pred, const float*
         prediction_loss_kernel<1><<<blocks, kLossThreads, 0, st>>>(y_pred, y, dy, (double*)workspace, n, (float)sp);
     int e = (int)cudaGetLastError();
     if (e != 0) return note_cuda_error("prediction_loss_kernel", e);
-    dynamics_loss_reduce_kernel<<<1, 256, 0, st>>>((const double*)workspace, blocks, sp, 0.0, loss);
+    dynamics_loss_reduce_kernel<<<1, 256, 0, st>>>((const double*)workspace, blocks, sp, 0.0, loss, 1);
     e = (int)cudaGetLastError();
     return e != 0 ? note_cuda_error("dynamics_loss_reduce_kernel", e) : IRBFN_OK;
 }
