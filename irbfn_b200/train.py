@@ -252,7 +252,9 @@ def _local_grad(state: TrainState, x: torch.Tensor, y: torch.Tensor, gb: int, lo
     B = int(x.shape[0])
     if state.gate_buf is None or state.gate_buf.shape[0] != B:
         state.gate_buf = torch.empty((B, m.num_regions), device=dev, dtype=torch.float32)
-    sparse_fwd = state.sparse_forward and B < (1 << 31)
+    # the gate-sparse forward pays its binning pass and the backward's own gate pass back only on large shards
+    # (27 x 500 x 8 -> 10, scripts/dev_o10_shard.py: 3.97 vs 4.26 ms at 262,144 samples, 1.46 vs 0.66 ms at 32,768)
+    sparse_fwd = state.sparse_forward and (1 << 18) <= B < (1 << 31)
     if sparse_fwd:
         y_pred = ops.forward_sparse(x, centers, log_sigs, v["kernel"], v["bias"], gd=gd, basis=m._basis,
                                     tol_abs=state.fwd_tol_abs)

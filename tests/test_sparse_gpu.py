@@ -231,8 +231,9 @@ def test_gate_sparse_training_step_matches_the_dense_step(cuda_device):
     lo = np.array([min(b) for b in cfg["lower_bounds"]], np.float32)
     hi = np.array([max(b) for b in cfg["upper_bounds"]], np.float32)
     g = torch.Generator().manual_seed(3)
-    x = (torch.rand((20000, 8), generator=g) * torch.from_numpy(hi - lo) + torch.from_numpy(lo)).to(cuda_device)
-    y = torch.randn((20000, 2), generator=g).to(cuda_device)
+    n = 1 << 18                       # the gate-sparse forward is taken from 2^18 samples per shard on
+    x = (torch.rand((n, 8), generator=g) * torch.from_numpy(hi - lo) + torch.from_numpy(lo)).to(cuda_device)
+    y = torch.randn((n, 2), generator=g).to(cuda_device)
     dense = TrainState(net, dp, lr=1e-3, device=cuda_device)
     yscale = float(net.apply(dp, x).abs().max())
     for kw in (dict(gate_tol=GATE_TOL), dict(gate_tol=GATE_TOL, fwd_tol_abs=1e-6 * yscale)):
