@@ -100,6 +100,18 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
                 if (u >= num_units) break;
             }
             q0 = u * (32 * Q) + (long long)(tid & 31) * Q;      // beyond B on the first round: an empty unit
+        } else if (SPARSE && a.work_counter != nullptr) {
+            // SPARSE with chunk-staged parameters: the staging barriers keep the CTA together, so the CTA fetches its
+            // tiles from the counter (the first one is static).  Binned tiles differ several-fold in active regions; a
+            // static round-robin left the SMs 83 % busy on average at C5 (sm__cycles_active.avg / elapsed.max).
+            if (iter > 0) {
+                __syncthreads();                               // everyone has read s_tile of the previous round
+                if (tid == 0) s_tile = gridDim.x + atomicAdd(a.work_counter, 1u);
+                __syncthreads();
+                tile = s_tile;
+            }
+            if (tile >= a.num_tiles) break;
+            q0 = tile * TQ + (long long)tid * Q;
         } else if (STREAM) {
             // Streamed input: the rows of a tile are uploaded WHILE earlier tiles compute.  Tiles are handed out by a
             // counter (CTAs whose first rows arrived early take more tiles than those that had to wait), and a CTA
