@@ -340,7 +340,8 @@ class WCRBFNet(_IrbfnModule):
         streams (hostpath.HostPipeline).  ``streamed=True`` (outputs of at most 16 columns): ONE persistent launch whose
         query tiles wait for their piece of the upload and which stores y straight into the pinned host buffer
         (hostpath.StreamedPipeline) -- 8 % faster than the chunk pipeline on some boxes of this pool, 10 % slower on
-        others (the per-copy set-up cost of the host link decides), so it is opt-in."""
+        others (the per-copy set-up cost of the host link decides), so it is opt-in; ``streamed="auto"`` times both
+        once per (device, batch size) on the caller's buffers (``out`` must be given) and keeps the faster."""
         from .hostpath import HostPipeline, StreamedPipeline
         device = _default_device()
         p = _unwrap(params)
@@ -349,6 +350,30 @@ class WCRBFNet(_IrbfnModule):
         gd = self._gate_pack(device)
         if streamed and (self.out_features > 16 or not ops.upload_streamed_available()):
             streamed = False
+        if streamed == "auto":
+            # which pipeline wins depends on the box's host link (per-copy set-up cost): time both ONCE per (device,
+            # batch size) on the caller's own buffers and keep the faster.  Small batches take the chunk pipeline.
+            B = int(x.shape[0])
+            akey = ("auto", str(device), B)
+            if B < (1 << 18) or out is None:
+                streamed = False
+            elif akey in self._const:
+                streamed = self._const[akey]
+            else:
+                def _time(flag):
+                    for _ in range(3):
+                        self.apply_host(params, x, out=out, chunk=chunk, streamed=flag)
+                    torch.cuda.synchronize(device)
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    for _ in range(10):
+                        self.apply_host(params, x, out=out, chunk=chunk, streamed=flag)
+                    e1.record()
+                    torch.cuda.synchronize(device)
+                    return e0.elapsed_time(e1)
+                _time(True), _time(False)                       # first use of either pipeline: allocations, lazy loading
+                t_s, t_c = min(_time(True), _time(True)), min(_time(False), _time(False))
+                streamed = self._const[akey] = bool(t_s < 0.98 * t_c)
         if streamed:
             key = ("spipe", str(device), chunk)
             if key not in self._const:

@@ -308,6 +308,13 @@ def test_streamed_host_path_matches_the_device_resident_forward(cuda_device):
         assert torch.equal(yh, dense(xh)), name
         y_np = net.apply_host(dp, x.numpy()[:5001], chunk=chunk, streamed=True)
         assert np.array_equal(y_np, dense(x[:5001]).numpy()), name
+        if B >= (1 << 18):      # "auto" times both pipelines once on these buffers and keeps the faster; same values
+            for _ in range(2):
+                yh.fill_(float("nan"))
+                net.apply_host(dp, xh, out=yh, streamed="auto")
+                torch.cuda.synchronize()
+                assert torch.equal(yh, dense(xh)), name
+            assert ("auto", str(torch.device("cuda", torch.cuda.current_device())), B) in net._const
 
 
 def test_forward_also_writes_the_gate_for_the_backward(cuda_device):
