@@ -240,6 +240,11 @@ _ws_cache = {}
 def _workspace(nbytes: int, device) -> Optional[torch.Tensor]:
     if nbytes == 0:
         return None
+    if torch.cuda.is_current_stream_capturing():
+        # under CUDA-graph capture the scratch comes from the capturing graph's own memory pool and is NOT cached:
+        # every captured graph keeps its own workspace (torch's captures share one capture stream, so a cache keyed by
+        # stream would hand two graphs the same buffer -- a race if they are ever replayed on different streams)
+        return torch.empty(nbytes, device=device, dtype=torch.uint8)
     key = (torch.device(device), torch.cuda.current_stream(device).cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:

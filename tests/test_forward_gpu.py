@@ -313,7 +313,8 @@ def test_streamed_host_path_matches_the_device_resident_forward(cuda_device):
                 yh.fill_(float("nan"))
                 net.apply_host(dp, xh, out=yh, streamed="auto")
                 torch.cuda.synchronize()
-                assert torch.equal(yh, dense(xh)), name
+                # (the chunk pipeline's ragged last chunk takes the split-over-kernels path: rounding, not bit equality)
+                assert rel_max(yh.numpy(), dense(xh).numpy().astype(np.float64)) < 2e-6, name
             assert ("auto", str(torch.device("cuda", torch.cuda.current_device())), B) in net._const
 
 
