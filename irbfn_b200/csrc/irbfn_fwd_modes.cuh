@@ -120,16 +120,22 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
             // the kernel's lifetime and ptxas hoists such loads above the barrier that follows the wait.
             __syncthreads();                                   // everyone has consumed s_tile of the previous round
             if (tid == 0) {
-                const unsigned t = atomicAdd(a.work_counter, 1u);
+                unsigned t = atomicAdd(a.work_counter, 1u);
                 if (t < (unsigned)a.num_tiles) {
                     const long long t0 = clock64();
                     unsigned v;
                     const unsigned* f = a.ready + t / (unsigned)a.tiles_per_flag;   // the flag of the tile's upload piece
-                    for (;;) {
+                    for (unsigned spin = 0;; ++spin) {
                         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
                         if (v != 0u) break;
-                        if (clock64() - t0 > 6000000000ll) {           // ~3 s: the upload never came
+                        // ~0.5 s: the upload never came.  The first CTA to find out raises the status word and every
+                        // CTA gives the launch up when it sees it (the result is undefined from here on), so a
+                        // stalled upload costs one budget, not one per tile.
+                        const bool gave_up = a.stream_status != nullptr && (spin & 63u) == 63u &&
+                                             *(volatile int*)a.stream_status != 0;
+                        if (gave_up || clock64() - t0 > 1000000000ll) {
                             if (a.stream_status != nullptr) atomicExch(a.stream_status, 1);
+                            t = 0xffffffffu;
                             break;
                         }
                         __nanosleep(128);

@@ -160,8 +160,22 @@ class StreamedPipeline:
         self.xd = None
         self.flags = None
         self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.status_host = torch.zeros(1, dtype=torch.int32).pin_memory()   # copied behind every launch
         self._pin_in = None
         self._pin_out = None
+
+    def check(self, wait: bool = True) -> None:
+        """Raise if an earlier call's kernel gave up on an upload piece (its result is then undefined).  The status
+        word is sticky on the device -- later launches give up at their first wait -- until this clears it.  With
+        wait=False only a call that has already finished is looked at (run() does that for the call before it)."""
+        if wait:
+            self.ev_done.synchronize()
+        elif not self.ev_done.query():
+            return
+        if int(self.status_host[0]) != 0:
+            self.status.zero_()
+            self.status_host.zero_()
+            raise RuntimeError("irbfn_forward_streamed: an upload piece never arrived (the kernel gave the launch up)")
 
     def _pinned_in(self, x):
         if isinstance(x, torch.Tensor) and x.is_pinned() and x.dtype == torch.float32 and x.is_contiguous():
@@ -177,6 +191,7 @@ class StreamedPipeline:
 
     def run(self, x, out, launch):
         """launch(x_dev, y_host, ready, queries_per_flag, status) enqueues ops.forward_streamed on the current stream."""
+        self.check(wait=False)
         xin = self._pinned_in(x)
         B = xin.shape[0]
         if xin.dim() != 2 or xin.shape[1] != self.D:
@@ -204,10 +219,9 @@ class StreamedPipeline:
         for s in self.s_ins:
             s.wait_event(self.ev_zero)
         ops.upload_streamed(xin, self.xd[:B], self.flags[:n + 1], self.chunk, self.s_ins)
+        self.status_host.copy_(self.status, non_blocking=True)
         self.ev_done.record(cur)                    # kernel finished => every upload finished and every y row stored
         if ret_numpy:
-            cur.synchronize()
-            if int(self.status.item()) != 0:
-                raise RuntimeError("irbfn_forward_streamed: an upload piece never arrived")
+            self.check()
             return out.numpy().copy()
         return out

@@ -371,9 +371,20 @@ class WCRBFNet(_IrbfnModule):
                     e1.record()
                     torch.cuda.synchronize(device)
                     return e0.elapsed_time(e1)
-                _time(True), _time(False)                       # first use of either pipeline: allocations, lazy loading
-                t_s, t_c = min(_time(True), _time(True)), min(_time(False), _time(False))
-                streamed = self._const[akey] = bool(t_s < 0.98 * t_c)
+                # first use of either pipeline: allocations, lazy loading.  A streamed call whose upload never arrived
+                # (status word: a profiler serialising the kernel against the copy streams) rules that path out.
+                self.apply_host(params, x, out=out, chunk=chunk, streamed=True)
+                try:
+                    self._const[("spipe", str(device), chunk)].check()
+                    usable = True
+                except RuntimeError:
+                    usable = False
+                if not usable:
+                    streamed = self._const[akey] = False
+                else:
+                    _time(True), _time(False)
+                    t_s, t_c = min(_time(True), _time(True)), min(_time(False), _time(False))
+                    streamed = self._const[akey] = bool(t_s < 0.98 * t_c)
         if streamed:
             key = ("spipe", str(device), chunk)
             if key not in self._const:

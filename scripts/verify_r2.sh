@@ -9,7 +9,7 @@ python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke_${TAG}.log 2>&1; e
 python bench.py > $O/bench_${TAG}_n1.json 2> $O/bench_${TAG}_n1.err
 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_${TAG}_reference.json 2> $O/bench_${TAG}_ref.err
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu"
-ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file $O/launches_${TAG}.csv $CMD > $O/ncu_launches_${TAG}.log 2>&1
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file $O/launches_${TAG}.csv $CMD > $O/ncu_launches_${TAG}.log 2>&1
 bash scripts/profile_fwd.sh ${TAG}
 # gate-sparse parameter-gradient kernel (C3 shape) and gate-sparse input-gradient kernel (C4 shape)
 ncu --set full --clock-control none --import-source on -k regex:irbfn_bwd_p_kernel -s 170 -c 1 -o $O/prof_bwdps_${TAG} -f \

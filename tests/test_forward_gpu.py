@@ -318,6 +318,44 @@ def test_streamed_host_path_matches_the_device_resident_forward(cuda_device):
             assert ("auto", str(torch.device("cuda", torch.cuda.current_device())), B) in net._const
 
 
+def test_streamed_forward_gives_up_when_an_upload_never_arrives(cuda_device):
+    """irbfn_forward_streamed whose second piece is never flagged: the launch ends within about one wait budget (not
+    one per tile) with the status word raised, a launch that finds the word still raised gives up at once, and after
+    clearing it the same buffers work again (include/irbfn_b200.h, `status`)."""
+    import os
+    import time
+    from conftest import GOLDEN_DIR
+    ops = _ops()
+    dev = cuda_device
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    rb, lin = params["rbf_list"], params["linear"]
+    c, ls = _t(rb["centers"], dev), _t(rb["log_sigs"], dev)
+    W, b = _t(lin["kernel"], dev), _t(lin["bias"], dev)
+    gd = _gd(cfg, dev)
+    basis = orc.BASIS_IDS[cfg["basis_func"]]
+    B, piece = 600 * 1024, 300 * 1024               # 600 tiles on 148 CTAs: several waits per CTA
+    x = _big_queries(arr, B, dev, 11)
+    y = torch.zeros((B, cfg["out_features"]), device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ready = torch.zeros(3, dtype=torch.int32, device=dev)
+    ready[0] = 1                                     # piece 0 "arrived", piece 1 never does
+    for _ in range(2):                               # the second launch finds the status word still raised
+        ready[2] = 0
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ops.forward_streamed(x, c, ls, W, b, y, ready, piece, gd=gd, basis=basis, status=status)
+        torch.cuda.synchronize()
+        assert time.perf_counter() - t0 < 2.5
+        assert int(status.item()) == 1
+    status.zero_()
+    ready[:2] = 1
+    ready[2] = 0
+    ops.forward_streamed(x, c, ls, W, b, y, ready, piece, gd=gd, basis=basis, status=status)
+    torch.cuda.synchronize()
+    assert int(status.item()) == 0
+    assert torch.equal(y, ops.forward(x, c, ls, W, b, gd=gd, basis=basis, split=False))
+
+
 def test_forward_also_writes_the_gate_for_the_backward(cuda_device):
     """irbfn_forward_gate: same y as irbfn_forward, and the gate it writes is the tanh gate (model.py:70-95);
     the backward fed with it as an external gate gives the parameter gradients of the descriptor form."""
