@@ -454,13 +454,21 @@ int irbfn_lattice_queries(const float* values, const int32_t* offset, const int3
  * q (B,num_dims); index (B,num_dims) int32.  Index-exact with numpy.searchsorted on the SAME float32 keys and
  * queries (NaN sorts last).  The reference bisects float64 table keys with float64 values: a value within
  * float32 rounding of a key can land in the neighbouring cell once both are narrowed to float32 -- callers
- * that need float64 cell boundaries pre-narrow their keys with nextafter towards the cell they want.
+ * that need the reference's float64 cell boundaries use irbfn_grid_index_f64 below.
  * irbfn_nearest_row compares float32 SQUARED distances with a strict <, rows in increasing order (lowest
  * index wins exact ties of the squared distance); the reference takes argmin of float32 norms, where the
  * square root can merge two distinct squared distances into one value and hand the tie to the lower index.
  */
 int irbfn_grid_index(const float* q, const float* keys, const int32_t* offset, int32_t* index,
                      int64_t B, int num_dims, irbfn_stream_t stream);
+
+/*
+ * irbfn_grid_index_f64: the same lookup on float64 keys and float64 values -- what explicit_planner.py:165-175
+ * bisects (the table's keys are float64 arrays, the query a float64 NumPy row), so the cell is the reference's for
+ * every input, including values within float32 rounding of a key.  HBM-bound either way.
+ */
+int irbfn_grid_index_f64(const double* q, const double* keys, const int32_t* offset, int32_t* index,
+                         int64_t B, int num_dims, irbfn_stream_t stream);
 
 /*
  * irbfn_nearest_row: index[b] = argmin_n || table[n,:] - q[b,:] ||_2 (first minimum wins), the

@@ -42,13 +42,15 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const float* __restric
 }
 
 // searchsorted(keys_d, v, side="right") = number of keys <= v, then min(len_d - 1, .)
-__global__ void __launch_bounds__(256) grid_index_kernel(const float* __restrict__ q, const float* __restrict__ keys,
+// T = float (tables narrowed to fp32) or double (the reference's float64 tables and values: index-exact).
+template <typename T>
+__global__ void __launch_bounds__(256) grid_index_kernel(const T* __restrict__ q, const T* __restrict__ keys,
                                                          const int* __restrict__ offset, int* __restrict__ out,
                                                          long long B, int nd) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= B * nd) return;
     const int d = (int)(t % nd);
-    const float v = __ldg(q + t);
+    const T v = __ldg(q + t);
     const int lo0 = __ldg(offset + d), hi0 = __ldg(offset + d + 1);
     int lo = lo0, hi = hi0;                     // first position with key > v
     while (lo < hi) {
@@ -224,16 +226,27 @@ extern "C" int irbfn_gather_rows(const float* X, const float* Y, const int64_t* 
     return e == cudaSuccess ? IRBFN_OK : note_cuda_error("gather_rows_kernel", (int)e);
 }
 
-extern "C" int irbfn_grid_index(const float* q, const float* keys, const int32_t* offset, int32_t* index,
-                                int64_t B, int num_dims, irbfn_stream_t stream) {
+template <typename T>
+static int grid_index_impl(const T* q, const T* keys, const int32_t* offset, int32_t* index, int64_t B, int num_dims,
+                           irbfn_stream_t stream) {
     if (B < 0 || num_dims <= 0) return IRBFN_ERR_BAD_DIMS;
     if (B == 0) return IRBFN_OK;
     if (!q || !keys || !offset || !index) return IRBFN_ERR_NULL_POINTER;
     const long long total = (long long)B * num_dims;
-    grid_index_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(q, keys, offset, index, B,
-                                                                                        num_dims);
+    grid_index_kernel<T><<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(q, keys, offset, index, B,
+                                                                                           num_dims);
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? IRBFN_OK : note_cuda_error("grid_index_kernel", (int)e);
+}
+
+extern "C" int irbfn_grid_index(const float* q, const float* keys, const int32_t* offset, int32_t* index,
+                                int64_t B, int num_dims, irbfn_stream_t stream) {
+    return grid_index_impl<float>(q, keys, offset, index, B, num_dims, stream);
+}
+
+extern "C" int irbfn_grid_index_f64(const double* q, const double* keys, const int32_t* offset, int32_t* index,
+                                    int64_t B, int num_dims, irbfn_stream_t stream) {
+    return grid_index_impl<double>(q, keys, offset, index, B, num_dims, stream);
 }
 
 extern "C" size_t irbfn_nearest_row_workspace_bytes(int64_t B, int64_t N) {
