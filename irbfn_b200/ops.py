@@ -591,28 +591,37 @@ class GridKeys:
     """Sorted per-dimension key arrays of an explicit table (ExplicitPlanner.input_keys,
     explicit_planner.py:165-175), packed flat on one device."""
 
-    def __init__(self, keys: Sequence[Sequence[float]], device):
+    def __init__(self, keys: Sequence[Sequence[float]], device, dtype=torch.float32):
+        """dtype=torch.float64 keeps the reference's float64 keys (the table's NumPy arrays): grid_index on float64
+        queries is then index-exact for every value, also those within float32 rounding of a key."""
         self.device = torch.device(device)
         self.lengths = [len(k) for k in keys]
         if not keys or min(self.lengths) == 0:
             raise ValueError("every dimension needs at least one key")
+        if dtype not in (torch.float32, torch.float64):
+            raise ValueError("GridKeys dtype must be torch.float32 or torch.float64")
+        npdt = np.float32 if dtype == torch.float32 else np.float64
         offs = np.concatenate([[0], np.cumsum(self.lengths)]).astype(np.int32)
-        self.keys = torch.tensor(np.concatenate([np.asarray(k, np.float32) for k in keys]), device=self.device)
+        self.keys = torch.tensor(np.concatenate([np.asarray(k, npdt) for k in keys]), device=self.device)
         self.offset = torch.tensor(offs, device=self.device)
         self.num_dims = len(keys)
 
 
 def grid_index(q, gk: GridKeys):
-    """(B, num_dims) int32 grid indices: min(len_d - 1, searchsorted(keys_d, q[:, d], 'right'))."""
+    """(B, num_dims) int32 grid indices: min(len_d - 1, searchsorted(keys_d, q[:, d], 'right')).  q has the dtype of
+    the keys: float32 (irbfn_grid_index) or float64 (irbfn_grid_index_f64, the reference's own precision)."""
     lib = _lib.load()
-    _chk(q, "q")
+    if not (isinstance(q, torch.Tensor) and q.is_cuda and q.is_contiguous() and q.dim() == 2
+            and q.dtype == gk.keys.dtype):
+        raise ValueError("q must be a contiguous 2-D CUDA tensor of the keys' dtype (%s)" % gk.keys.dtype)
     B, nd = q.shape
     if nd != gk.num_dims:
         raise ValueError("q has %d columns, the grid has %d dimensions" % (nd, gk.num_dims))
     out = torch.empty((B, nd), device=q.device, dtype=torch.int32)
     if B > 0:
+        fn = lib.irbfn_grid_index if q.dtype == torch.float32 else lib.irbfn_grid_index_f64
         with torch.cuda.device(q.device):
-            rc = lib.irbfn_grid_index(_ptr(q), _ptr(gk.keys), _ptr(gk.offset), _ptr(out), B, nd, _stream())
+            rc = fn(_ptr(q), _ptr(gk.keys), _ptr(gk.offset), _ptr(out), B, nd, _stream())
         _lib.check(rc, "irbfn_grid_index")
     return out
 

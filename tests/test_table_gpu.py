@@ -129,6 +129,31 @@ def test_grid_index_matches_searchsorted(cuda_device):
     assert out.dtype == torch.int32 and np.array_equal(out.cpu().numpy(), ref)
 
 
+def test_grid_index_f64_is_index_exact_where_float32_keys_are_not(cuda_device):
+    """irbfn_grid_index_f64: float64 keys and values, as explicit_planner.py:165-175 bisects them.  Keys that are not
+    representable in float32 and values one float64 ulp either side of a key: the float64 entry point gives numpy's
+    cell for every value; the float32 one (same inputs narrowed) provably does not on these."""
+    rng = np.random.default_rng(9)
+    keys = [np.sort(rng.uniform(-3, 3, n)) + 1e-9 for n in (20, 1, 7, 33)]        # float64, off the float32 lattice
+    assert all((k.astype(np.float32).astype(np.float64) != k).all() for k in keys)
+    q = rng.uniform(-4, 4, (20000, 4))
+    for d, k in enumerate(keys):                                                   # at, just below, just above keys
+        pick = k[rng.integers(0, len(k), 3000)]
+        q[:3000, d] = pick
+        q[3000:6000, d] = np.nextafter(pick, -np.inf)
+        q[6000:9000, d] = np.nextafter(pick, np.inf)
+    q[7, 2] = np.nan
+    ref = tor.grid_index(q, keys)
+    gk = ops.GridKeys(keys, cuda_device, dtype=torch.float64)
+    out = ops.grid_index(torch.tensor(q, device=cuda_device), gk)
+    assert out.dtype == torch.int32 and np.array_equal(out.cpu().numpy(), ref)
+    out32 = ops.grid_index(_dev(q.astype(np.float32), cuda_device), ops.GridKeys(keys, cuda_device))
+    assert not np.array_equal(out32.cpu().numpy(), ref)       # why the float64 entry point exists
+    with pytest.raises(ValueError):                            # dtypes of keys and values must agree
+        ops.grid_index(_dev(q.astype(np.float32), cuda_device), gk)
+    assert ops.grid_index(torch.empty((0, 4), device=cuda_device, dtype=torch.float64), gk).shape == (0, 4)
+
+
 def test_table_errors(cuda_device):
     q = torch.zeros((4, 8), device=cuda_device)
     with pytest.raises(ValueError):

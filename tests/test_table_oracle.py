@@ -34,6 +34,9 @@ def test_table_entry_points_validate_before_touching_a_device():
     assert lib.irbfn_gather_rows(one, one, one, one, one, 0, 10, 8, 2, one, None) == 0
     assert lib.irbfn_gather_rows(one, None, one, one, one, 4, 10, 8, 2, one, None) == -4
     assert lib.irbfn_grid_index(one, one, one, one, 4, 0, None) == -1
+    assert lib.irbfn_grid_index_f64(one, one, one, one, 4, 0, None) == -1
+    assert lib.irbfn_grid_index_f64(one, None, one, one, 4, 2, None) == -4
+    assert lib.irbfn_grid_index_f64(one, one, one, one, 0, 2, None) == 0
     assert lib.irbfn_nearest_row(one, one, one, None, 4, 0, 8, None, 0, None) == -1
     assert lib.irbfn_nearest_row(one, one, one, None, 4, 10, 9, None, 0, None) == -2
     assert lib.irbfn_nearest_row(one, one, one, None, 0, 10, 8, None, 0, None) == 0
