@@ -148,7 +148,7 @@ int irbfn_forward_gate(const float* x, const float* centers, const float* log_si
  *   ready    device uint32: ceil(B / queries_per_flag) flags followed by ONE tile-counter word; ALL ZERO when this call
  *            is enqueued (and not written by a copy stream before that)
  *   queries_per_flag   a multiple of 1,024
- *   status   optional device int, ZERO on entry; set to 1 if a piece did not arrive within ~0.5 s (e.g. under a
+ *   status   optional device int, ZERO on entry; set to 1 if a piece did not arrive within ~2 s (e.g. under a
  *            profiler that serialises the kernel against the copy streams).  The whole launch is then given up -- every
  *            CTA stops at its next wait -- and y is undefined.  The word is sticky: a launch that finds it non-zero
  *            gives up at its first wait, until the caller clears it.

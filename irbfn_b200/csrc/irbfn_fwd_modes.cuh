@@ -128,12 +128,12 @@ __global__ void __launch_bounds__(NT, 1) irbfn_fwd_mode_kernel(const FwdArgs a) 
                     for (unsigned spin = 0;; ++spin) {
                         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
                         if (v != 0u) break;
-                        // ~0.5 s: the upload never came.  The first CTA to find out raises the status word and every
+                        // ~2 s: the upload never came.  The first CTA to find out raises the status word and every
                         // CTA gives the launch up when it sees it (the result is undefined from here on), so a
                         // stalled upload costs one budget, not one per tile.
                         const bool gave_up = a.stream_status != nullptr && (spin & 63u) == 63u &&
                                              *(volatile int*)a.stream_status != 0;
-                        if (gave_up || clock64() - t0 > 1000000000ll) {
+                        if (gave_up || clock64() - t0 > 4000000000ll) {
                             if (a.stream_status != nullptr) atomicExch(a.stream_status, 1);
                             t = 0xffffffffu;
                             break;

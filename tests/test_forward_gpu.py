@@ -345,7 +345,7 @@ def test_streamed_forward_gives_up_when_an_upload_never_arrives(cuda_device):
         t0 = time.perf_counter()
         ops.forward_streamed(x, c, ls, W, b, y, ready, piece, gd=gd, basis=basis, status=status)
         torch.cuda.synchronize()
-        assert time.perf_counter() - t0 < 2.5
+        assert time.perf_counter() - t0 < 5.0
         assert int(status.item()) == 1
     status.zero_()
     ready[:2] = 1
