@@ -253,11 +253,22 @@ def main():
     # query tiles wait for their piece of the upload and which stores y straight into the pinned host buffer
     # (irbfn_forward_streamed) -- which of the two wins depends on the box's host link, so the call times both once
     # (outside the timed region: the warm-up steps) and keeps the faster; both fixed choices are reported beside it
-    ms_e2e = timed(lambda i: net.apply_host(params, xh, out=yh, streamed="auto"), args.steps, args.warmup)
+    e2e_mode, e2e_errors = ["auto"], []
+
+    def e2e_step(i):        # a launch that gave up on its upload is raised one call later: finish the run on chunks
+        try:
+            net.apply_host(params, xh, out=yh, streamed=e2e_mode[0])
+        except RuntimeError as exc:
+            e2e_errors.append(str(exc))
+            e2e_mode[0] = False
+            net.apply_host(params, xh, out=yh, streamed=False)
+    ms_e2e = timed(e2e_step, args.steps, args.warmup)
     e2e = {"value": world * B / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
            "h2d_bytes_per_step": int(xh.numel() * 4), "d2h_bytes_per_step": int(yh.numel() * 4),
            "ms_per_step_chunk_pipeline": timed(lambda i: net.apply_host(params, xh, out=yh, streamed=False),
                                                args.steps, args.warmup)}
+    if e2e_errors:
+        e2e["error_during_timed_region"] = e2e_errors[0]
     if ops.upload_streamed_available():
         e2e["auto_chose"] = "streamed" if net._const.get(("auto", str(dev), B)) else "chunks"
         gave_up = []
