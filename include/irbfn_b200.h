@@ -125,6 +125,24 @@ int irbfn_forward(const float* x, const float* centers, const float* log_sigs, c
                   void* workspace, size_t workspace_bytes, irbfn_stream_t stream);
 
 /*
+ * Which kernel irbfn_forward runs for a shape (a host-side query; nothing is launched).  y_only: the call asks for
+ * y alone (no hidden activations, not irbfn_forward_gate / _streamed).
+ *   IRBFN_PATH_TILED  the query-stationary throughput kernel, one CTA per 1,024-query tile
+ *   IRBFN_PATH_SPLIT  the same with every region's kernels split over CTAs and a fixed-order reduction of the
+ *                     partial outputs (needs the workspace; without it the tiled kernel runs)
+ *   IRBFN_PATH_SMALL  the latency kernel of pred_step (src/irbfn_mpc/irbfn_planner.py:29-32: one query per control
+ *                     step; 400 in the notebooks): a CTA owns one or four queries and its threads share the
+ *                     (region, kernel) pairs; ONE launch, no workspace.  Taken when y_only, O <= 16,
+ *                     R*K <= 16,384 and B*R*K <= 5*2^20.
+ * All three give the same y within the forward's tolerance (the summation order over kernels differs); each is
+ * deterministic run to run.  Negative: an IRBFN_ERR_* code.
+ */
+#define IRBFN_PATH_TILED 0
+#define IRBFN_PATH_SPLIT 1
+#define IRBFN_PATH_SMALL 2
+int irbfn_forward_path(int64_t B, int R, int K, int D, int O, int y_only);
+
+/*
  * Training-step forward: irbfn_forward with the tanh gate, which also writes the gate gamma (B,R) it
  * computes on the fly (model.py:70-95).  Handing that buffer to irbfn_backward as its external `gate`
  * (gd = NULL) saves the backward's own gate pass -- what jax.value_and_grad's forward residuals would

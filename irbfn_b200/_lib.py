@@ -15,6 +15,7 @@ BASIS_GAUSSIAN = 0
 BASIS_INVERSE_QUADRATIC = 1
 MAX_D = 8
 MAX_S = 8
+PATH_TILED, PATH_SPLIT, PATH_SMALL = 0, 1, 2      # irbfn_forward_path
 
 GRAD_CENTERS = 0x01
 GRAD_LOG_SIGS = 0x02
@@ -35,7 +36,7 @@ EXPORTED_SYMBOLS = (
     "irbfn_backward_workspace_bytes", "irbfn_backward", "irbfn_backward_sparse", "irbfn_region_gate",
     "irbfn_softmax_gate", "irbfn_forward_plan",
     "irbfn_dynamics_loss_workspace_bytes", "irbfn_dynamics_loss", "irbfn_integrate", "irbfn_jacobian", "irbfn_jacobian_sparse_workspace_bytes", "irbfn_jacobian_sparse",
-    "irbfn_gather_rows", "irbfn_lattice_queries", "irbfn_grid_index", "irbfn_grid_index_f64", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
+    "irbfn_gather_rows", "irbfn_lattice_queries", "irbfn_grid_index", "irbfn_grid_index_f64", "irbfn_forward_path", "irbfn_nearest_row_workspace_bytes", "irbfn_nearest_row",
     "irbfn_prediction_loss_workspace_bytes", "irbfn_prediction_loss",
     "irbfn_clip_adam_workspace_bytes", "irbfn_clip_adam",
     "irbfn_fused_update_max_n", "irbfn_fused_update_buffer_bytes", "irbfn_fused_update",
@@ -146,6 +147,8 @@ def load():
     lib.irbfn_lattice_queries.argtypes = [p, p, p, i, p, p, i64, i, p]
     lib.irbfn_grid_index.restype = i
     lib.irbfn_grid_index.argtypes = [p, p, p, p, i64, i, p]
+    lib.irbfn_forward_path.restype = i
+    lib.irbfn_forward_path.argtypes = [i64, i, i, i, i, i]
     lib.irbfn_grid_index_f64.restype = i
     lib.irbfn_grid_index_f64.argtypes = [p, p, p, p, i64, i, p]
     lib.irbfn_nearest_row_workspace_bytes.restype = sz

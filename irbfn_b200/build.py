@@ -41,7 +41,7 @@ def _units():
             continue
         for d in FEATURE_COUNTS:
             units.append((name, ["-DIRBFN_D=%d" % d], "%s_d%d.o" % (name[:-3], d)))
-    for name in ("irbfn_bwd_api.cu", "irbfn_jac_api.cu", "irbfn_sparse.cu"):
+    for name in ("irbfn_bwd_api.cu", "irbfn_jac_api.cu", "irbfn_sparse.cu", "irbfn_fwd_small.cu"):
         if os.path.exists(os.path.join(CSRC, name)):
             units.append((name, [], name[:-3] + ".o"))
     return units

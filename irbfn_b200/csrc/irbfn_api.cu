@@ -23,6 +23,7 @@ int launch_fwd_d5(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d6(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d7(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_fwd_d8(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
+int launch_fwd_small(const FwdSmallArgs&, int basis, cudaStream_t);               // irbfn_fwd_small.cu
 int launch_fwdm_d4(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);   // gate-writing / gate-sparse variants
 int launch_fwdm_d5(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
 int launch_fwdm_d6(const FwdArgs&, int, int, int, int, size_t, cudaStream_t);
@@ -220,6 +221,15 @@ size_t irbfn_forward_workspace_bytes(int64_t B, int R, int K, int D, int O, int 
     return ns > 1 ? (size_t)ns * (size_t)B * (size_t)O * sizeof(float) : 0;
 }
 
+int irbfn_forward_path(int64_t B, int R, int K, int D, int O, int y_only) {
+    if (B <= 0 || R <= 0 || K <= 0 || D <= 0 || D > IRBFN_MAX_D || O < 0) return IRBFN_ERR_BAD_DIMS;
+    if (y_only && fwd_small_applies(B, R, K, D, O)) return IRBFN_PATH_SMALL;
+    int sms = 148, smem = 0;
+    device_info(&sms, &smem);   // keeps the nominal B200 value when no device is present
+    int kps;
+    return fwd_split(B, R, K, sms, &kps) > 1 && O > 0 ? IRBFN_PATH_SPLIT : IRBFN_PATH_TILED;
+}
+
 static int forward_impl(const float* x, const float* centers, const float* log_sigs, const float* W,
                         const float* bias, const float* gate, const IrbfnGateDesc* gd, float* y,
                         float* hidden, float* gate_out, int64_t B, int R, int K, int D, int O, int basis,
@@ -266,6 +276,27 @@ static int forward_impl(const float* x, const float* centers, const float* log_s
     rc = query_device(&dev);
     if (rc != IRBFN_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
+
+    // A few queries against a small parameter set (pred_step): the pair-parallel kernel, one launch, no workspace.
+    if (y != nullptr && hidden == nullptr && gate_out == nullptr && ready == nullptr &&
+        fwd_small_applies(B, R, K, D, O)) {
+        FwdSmallArgs sa{};
+        sa.x = x;
+        sa.centers = centers;
+        sa.log_sigs = log_sigs;
+        sa.W = W;
+        sa.bias = bias;
+        sa.gate_ext = gate;
+        sa.gd = gdev;
+        sa.y = y;
+        sa.B = B;
+        sa.R = R;
+        sa.K = K;
+        sa.D = D;
+        sa.O = O;
+        const int e = launch_fwd_small(sa, basis, st);
+        return e == 0 ? IRBFN_OK : note_cuda_error("irbfn_fwd_small_kernel", e);
+    }
 
     const int DT = D < 4 ? 4 : D;  // compiled feature count; extra columns are zero padding
     const int Ototal = y ? O : 0;

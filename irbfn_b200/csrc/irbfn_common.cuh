@@ -299,6 +299,20 @@ struct FwdArgs {
     int* stream_status;     // set to 1 if a flag did not arrive within the spin budget (the result is then undefined)
 };
 
+// Arguments of the small-batch (pair-parallel) forward, irbfn_fwd_small.cu.
+struct FwdSmallArgs {
+    const float* x;          // (B,D)
+    const float* centers;    // (R,K,D)
+    const float* log_sigs;   // (R,K)
+    const float* W;          // (K,O)
+    const float* bias;       // (O)
+    const float* gate_ext;   // (B,R) or nullptr
+    GateDev gd;              // used when gate_ext == nullptr
+    float* y;                // (B,O)
+    long long B;
+    int R, K, D, O;
+};
+
 // log-sigma -> the per-kernel scale used in the hot loop.
 //   gaussian         : phi = exp(-d2 / sigma^2) = ex2(d2 * nscale),  nscale = -exp(-2 ls) * log2(e)
 //   inverse quadratic: phi = 1 / (1 + d2 / sigma^2) = rcp(fma(d2, scale, 1)),  scale = exp(-2 ls)

@@ -27,6 +27,19 @@ inline int fwd_ot_for(int ocur) {
     return 16;
 }
 
+// Small-batch forward (irbfn_fwd_small.cu): a CTA owns a few queries and its threads share the (region, kernel)
+// pairs.  A CTA re-reads every parameter, so the parameter set must be small (it stays in L2) and the batch a few
+// hundred queries; beyond that the query-stationary kernel's register tiling wins (measured: scripts/dev_latency.py).
+constexpr long long kFwdSmallMaxPairs = 16384;        // R*K
+constexpr long long kFwdSmallMaxWork = 5ll << 20;     // B*R*K (C2 shape: up to 4,369 queries)
+constexpr long long kFwdSmallQ1MaxB = 148;            // one query per CTA up to one CTA per SM, then four per CTA
+inline bool fwd_small_applies(long long B, int R, int K, int D, int O) {
+    const long long pairs = (long long)R * K;
+    if (B <= 0 || O <= 0 || O > 16 || D > 8 || R > 2048 || K < 1) return false;
+    if (pairs > kFwdSmallMaxPairs) return false;
+    return B * pairs <= kFwdSmallMaxWork;
+}
+
 // Split of the kernels of every region over gridDim.y for batches that do not fill the device with one CTA
 // per 1,024-query tile.  Returns the number of splits (1 = none) and the kernels per split (multiple of
 // kFwdKT).  The choice minimises a cost model fitted to B200 measurements (scripts/dev_fwd_split.py), in

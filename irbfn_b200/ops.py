@@ -19,7 +19,7 @@ from ._lib import (BASIS_GAUSSIAN, BASIS_INVERSE_QUADRATIC, GRAD_CENTERS, GRAD_G
 __all__ = [
     "GatePack", "forward", "forward_sparse", "backward", "region_gate", "softmax_gate", 
     "dynamics_loss", "integrate", "default_dyn_params", "jacobian", "fused_update_", "fused_update_max_n", "lattice_queries",
-    "gather_rows", "GridKeys", "grid_index", "nearest_row",
+    "gather_rows", "GridKeys", "grid_index", "nearest_row", "forward_path",
     "BASIS_GAUSSIAN", "BASIS_INVERSE_QUADRATIC", "GRAD_CENTERS", "GRAD_LOG_SIGS", "GRAD_KERNEL",
     "GRAD_X", "GRAD_GATE", "GRAD_PARAMS",
 ]
@@ -86,6 +86,14 @@ class GatePack:
 
     def ref(self):
         return C.byref(self.desc)
+
+
+def forward_path(B: int, R: int, K: int, D: int, O: int, y_only: bool = True) -> str:
+    """Which kernel ``forward`` runs for a shape (irbfn_forward_path): "tiled" (throughput kernel), "split" (the same
+    with the kernels split over CTAs, small batches) or "small" (the pair-parallel latency kernel of pred_step)."""
+    rc = _lib.load().irbfn_forward_path(int(B), int(R), int(K), int(D), int(O), 1 if y_only else 0)
+    _lib.check(rc if rc < 0 else 0, "irbfn_forward_path")
+    return ("tiled", "split", "small")[rc]
 
 
 def forward(x, centers, log_sigs, kernel=None, bias=None, *, gate=None, gd: GatePack = None,

@@ -43,6 +43,11 @@ def test_forward_matches_golden(path, cuda_device):
     if cfg["kind"] == "wcrbf":
         y = ops.forward(x, _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(params["linear"]["kernel"], dev),
                         _t(params["linear"]["bias"], dev), gd=_gd(cfg, dev), basis=basis)
+        # the fixtures' few thousand queries take the latency kernel (irbfn_forward_path); asking for the hidden
+        # activations as well keeps the throughput kernel on every fixture too
+        y_t, _ = ops.forward(x, _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(params["linear"]["kernel"], dev),
+                             _t(params["linear"]["bias"], dev), gd=_gd(cfg, dev), basis=basis, want_hidden=True)
+        assert rel_max(y_t.cpu().numpy(), arr["y64"]) < OUT_TOL
     elif cfg["kind"] == "cluster":
         gate, logits = ops.softmax_gate(x, _t(params["cluster"]["kernel"], dev), _t(params["cluster"]["bias"], dev))
         assert rel_max(logits.cpu().numpy(), arr["logits64"]) < OUT_TOL
@@ -125,6 +130,11 @@ def test_forward_ragged_shapes_match_oracle(shape, basis, cuda_device):
                        _t(p["bias"], dev), gd=_gd(cfg, dev), basis=basis, want_hidden=True)
     assert rel_max(y.cpu().numpy(), y_ref) < OUT_TOL
     assert rel_max(h.cpu().numpy(), h_ref) < OUT_TOL
+    # y alone: these batches take the latency kernel where the output window allows (O <= 16)
+    assert ops.forward_path(B, R, K, D, O) == ("small" if O <= 16 else ops.forward_path(B, R, K, D, O, False))
+    y1 = ops.forward(_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev),
+                     _t(p["bias"], dev), gd=_gd(cfg, dev), basis=basis)
+    assert rel_max(y1.cpu().numpy(), y_ref) < OUT_TOL
     # the same through an externally supplied gate
     y2 = ops.forward(_t(x, dev), _t(p["centers"], dev), _t(p["log_sigs"], dev), _t(p["kernel"], dev),
                      _t(p["bias"], dev), gate=_t(gamma, dev), basis=basis)
@@ -226,18 +236,67 @@ def test_small_batch_split_over_kernels_matches_unsplit_and_oracle(B, cuda_devic
     lib = _lib.load()
     need = lib.irbfn_forward_workspace_bytes(B, 3, 250, 7, 10, 1)
     assert (need > 0) == (B <= 40000 and B * 2 <= 148 * 1024)
+    # (the hidden activations are asked for as well: y alone would take the latency kernel at the smaller sizes)
+    assert ops.forward_path(B, 3, 250, 7, 10, y_only=False) == ("split" if need > 0 else "tiled")
     y, h = ops.forward(xs, c, ls, W, b, gd=gd, basis=0, want_hidden=True)
-    y0 = torch.empty_like(y)
+    y0, h0 = torch.empty_like(y), torch.empty_like(h)
     rc = lib.irbfn_forward(C.c_void_p(xs.data_ptr()), C.c_void_p(c.data_ptr()), C.c_void_p(ls.data_ptr()),
                            C.c_void_p(W.data_ptr()), C.c_void_p(b.data_ptr()), None, gd.ref(),
-                           C.c_void_p(y0.data_ptr()), None, B, 3, 250, 7, 10, 0, None, 0,
+                           C.c_void_p(y0.data_ptr()), C.c_void_p(h0.data_ptr()), B, 3, 250, 7, 10, 0, None, 0,
                            C.c_void_p(torch.cuda.current_stream().cuda_stream))
     assert rc == 0
     assert rel_max(y.cpu().numpy(), y_ref) < OUT_TOL
     assert rel_max(y0.cpu().numpy(), y_ref) < OUT_TOL
     assert rel_max(h.cpu().numpy(), h_ref) < OUT_TOL
-    y2 = ops.forward(xs, c, ls, W, b, gd=gd, basis=0)
+    assert rel_max(h0.cpu().numpy(), h_ref) < OUT_TOL
+    y2, _ = ops.forward(xs, c, ls, W, b, gd=gd, basis=0, want_hidden=True)
     assert torch.equal(y, y2)          # fixed-order reduction: bit-identical run to run
+
+
+SMALL_SHAPES = [
+    # B, R, K, D, O: one query (pred_step), CTA-count edges (148 / 149: one vs four queries per CTA), K below and
+    # above the CTA's 256 threads, K = 1, many regions, every output window width
+    (1, 12, 100, 8, 2), (1, 1, 1000, 7, 2), (2, 4, 100, 5, 10), (5, 3, 1, 4, 1), (147, 2, 257, 6, 3),
+    (148, 12, 100, 8, 2), (149, 12, 100, 8, 2), (400, 1, 1000, 8, 10), (593, 5, 64, 3, 16), (1001, 7, 33, 8, 7),
+    (3, 500, 10, 8, 10), (4099, 12, 100, 8, 2), (7, 16, 1024, 6, 16),
+]
+
+
+@pytest.mark.parametrize("basis", [0, 1])
+@pytest.mark.parametrize("shape", SMALL_SHAPES, ids=["B%d_R%d_K%d_D%d_O%d" % s for s in SMALL_SHAPES])
+def test_latency_kernel_matches_oracle_and_the_throughput_kernel(shape, basis, cuda_device):
+    """The pair-parallel small-batch kernel (irbfn_fwd_small.cu; pred_step, irbfn_planner.py:29-32): against the
+    float64 oracle with the tanh gate and with an external gate, against the throughput kernel on the same inputs
+    (taken when the hidden activations are requested), bit-identical run to run, and it needs no workspace."""
+    import ctypes as C
+    from irbfn_b200 import _lib
+    ops = _ops()
+    B, R, K, D, O = shape
+    nb = (3, 2, 2) if R <= 12 else (8, 8, 8)
+    cfg, p, x = _synthetic(23, B, R, K, D, O, S=3, nb=nb)
+    dev = cuda_device
+    assert ops.forward_path(B, R, K, D, O) == "small"
+    gamma = orc.region_activation(x.astype(np.float64), R, cfg["lower_bounds"], cfg["upper_bounds"],
+                                  cfg["delta"], cfg["dimension_ranges"])
+    y_ref = orc.forward(x, p["centers"], p["log_sigs"], p["kernel"], p["bias"], gamma, basis)
+    xs, c, ls, W, b = (_t(a, dev) for a in (x, p["centers"], p["log_sigs"], p["kernel"], p["bias"]))
+    gd = _gd(cfg, dev)
+    y = ops.forward(xs, c, ls, W, b, gd=gd, basis=basis)
+    assert rel_max(y.cpu().numpy(), y_ref) < OUT_TOL
+    assert torch.equal(y, ops.forward(xs, c, ls, W, b, gd=gd, basis=basis))
+    y_t, _ = ops.forward(xs, c, ls, W, b, gd=gd, basis=basis, want_hidden=True)
+    assert rel_max(y.cpu().numpy(), y_t.cpu().numpy().astype(np.float64)) < OUT_TOL
+    y_g = ops.forward(xs, c, ls, W, b, gate=_t(gamma, dev), basis=basis)
+    assert rel_max(y_g.cpu().numpy(), y_ref) < OUT_TOL
+    # through the C ABI with no workspace at all, output bracketed by canaries
+    buf = torch.full((B + 2, O), 7.0, device=dev)
+    rc = _lib.load().irbfn_forward(C.c_void_p(xs.data_ptr()), C.c_void_p(c.data_ptr()), C.c_void_p(ls.data_ptr()),
+                                   C.c_void_p(W.data_ptr()), C.c_void_p(b.data_ptr()), None, gd.ref(),
+                                   C.c_void_p(buf[1:].data_ptr()), None, B, R, K, D, O, basis, None, 0,
+                                   C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert torch.equal(buf[1:B + 1], y) and bool((buf[0] == 7.0).all()) and bool((buf[B + 1] == 7.0).all())
 
 
 def test_host_pipeline_variants_agree(cuda_device):
@@ -257,22 +316,25 @@ def test_host_pipeline_variants_agree(cuda_device):
     xh = torch.from_numpy(x.copy()).pin_memory()
     yh = torch.empty((5000, 2)).pin_memory()
     ref = net.apply(dp, torch.from_numpy(x).to(cuda_device)).cpu()
+    first = None
     for kw in (dict(streamed=False), dict(), dict(streamed=True), dict(copy_streams=2), dict(graph=True), dict(graph=True),
                dict(run_streams=2), dict(run_streams=3, graph=True), dict(run_streams=3, graph=True)):
         yh.zero_()
         net.apply_host(dp, xh, out=yh, chunk=2048, **kw)
         torch.cuda.synchronize()
-        if kw.get("run_streams", 1) == 1 and not kw.get("streamed"):
-            assert torch.equal(yh, ref), kw
-        else:   # the streamed launch and several chunk kernels in flight run unsplit (one CTA per tile): another
-                # summation order than the split small-batch call behind `ref`
-            assert torch.allclose(yh, ref, rtol=0, atol=2e-6 * float(ref.abs().max())), kw
+        # 2,048-query chunks take the latency kernel, the streamed launch and several chunk kernels in flight the
+        # tiled one, the 5,000-query call behind `ref` the split one: three summation orders over the kernels
+        assert torch.allclose(yh, ref, rtol=0, atol=2e-6 * float(ref.abs().max())), kw
+        if first is None:
+            first = yh.clone()
+        elif kw.get("run_streams", 1) == 1 and not kw.get("streamed"):
+            assert torch.equal(yh, first), kw         # the chunk pipeline's variants agree to the bit
     xh.mul_(0.5)                                      # new values, same buffers: the graph must pick them up
     ref2 = net.apply(dp, xh.to(cuda_device)).cpu()
     net.apply_host(dp, xh, out=yh, chunk=2048, graph=True)
     torch.cuda.synchronize()
-    assert torch.equal(yh, ref2)
-    assert np.array_equal(net.apply_host(dp, x * 0.5, chunk=2048), ref2.numpy())
+    assert torch.allclose(yh, ref2, rtol=0, atol=2e-6 * float(ref2.abs().max()))
+    assert np.array_equal(net.apply_host(dp, x * 0.5, chunk=2048), yh.numpy())
 
 
 def test_streamed_host_path_matches_the_device_resident_forward(cuda_device):
@@ -296,8 +358,10 @@ def test_streamed_host_path_matches_the_device_resident_forward(cuda_device):
         xh = x.clone().pin_memory()
         yh = torch.full((B, cfg["out_features"]), float("nan")).pin_memory()
         rb, lin = dp["params"]["rbf_list"], dp["params"]["linear"]
+        # (hidden activations requested: the tiled kernel also for the 5,001-query call below)
         dense = lambda xx: ops.forward(xx.to(cuda_device), rb["centers"], rb["log_sigs"], lin["kernel"], lin["bias"],
-                                       gd=_gd(cfg, cuda_device), basis=orc.BASIS_IDS[cfg["basis_func"]], split=False).cpu()
+                                       gd=_gd(cfg, cuda_device), basis=orc.BASIS_IDS[cfg["basis_func"]], split=False,
+                                       want_hidden=True)[0].cpu()
         net.apply_host(dp, xh, out=yh, chunk=chunk, streamed=True)
         torch.cuda.synchronize()
         assert torch.equal(yh, dense(x)), name
@@ -368,10 +432,11 @@ def test_forward_also_writes_the_gate_for_the_backward(cuda_device):
         x = _t(arr["x"], dev)
         args = (x, _t(rb["centers"], dev), _t(rb["log_sigs"], dev), _t(lin["kernel"], dev), _t(lin["bias"], dev))
         gd = _gd(cfg, dev)
-        y0 = ops.forward(*args, gd=gd, basis=basis)
+        y0, _ = ops.forward(*args, gd=gd, basis=basis, want_hidden=True)     # the same (tiled / split) kernel family
         gate = torch.full((x.shape[0], cfg["num_regions"]), float("nan"), device=dev)
         y1 = ops.forward(*args, gd=gd, basis=basis, gate_out=gate)
         assert torch.equal(y0, y1)
+        assert rel_max(ops.forward(*args, gd=gd, basis=basis).cpu().numpy(), y1.cpu().numpy().astype(np.float64)) < OUT_TOL
         ref = orc.region_activation(arr["x"].astype(np.float64), cfg["num_regions"], cfg["lower_bounds"],
                                     cfg["upper_bounds"], cfg["delta"], cfg["dimension_ranges"])
         assert np.abs(gate.cpu().numpy() - ref).max() <= 5e-6

@@ -69,7 +69,8 @@ def test_noalloc_forward_matches_existing_entry_point_twice(name, cuda_device):
     used_scratch = False
     # two calls in a row with DIFFERENT batches (sizes that take the split path, so the scratch array is used and
     # the second call finds the first one's partial sums in it), then the first batch again
-    for B in (4096, 3001, 4096):
+    for B in (16384, 9001, 16384):
+        assert ops.forward_path(B, ls.shape[0], ls.shape[1], x0.shape[1], W.shape[1]) == "split"
         x = (torch.tensor(lo) + torch.rand((B, x0.shape[1]), generator=g) * torch.tensor(hi - lo)).to(dev).contiguous()
         y_new = torch.full((B, W.shape[1]), float("nan"), device=dev)
         y_old = torch.full((B, W.shape[1]), float("nan"), device=dev)
