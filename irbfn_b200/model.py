@@ -342,12 +342,22 @@ class WCRBFNet(_IrbfnModule):
         (hostpath.StreamedPipeline) -- 8 % faster than the chunk pipeline on some boxes of this pool, 10 % slower on
         others (the per-copy set-up cost of the host link decides), so it is opt-in; ``streamed="auto"`` times both
         once per (device, batch size) on the caller's buffers (``out`` must be given) and keeps the faster."""
-        from .hostpath import HostPipeline, StreamedPipeline
+        from .hostpath import HostPipeline, PredStepPipeline, StreamedPipeline
         device = _default_device()
         p = _unwrap(params)
         centers, log_sigs = self._rbf_leaves(p, device)
         kernel, bias = _leaf(p["linear"]["kernel"], device), _leaf(p["linear"]["bias"], device)
         gd = self._gate_pack(device)
+        rows = int(x.shape[0]) if getattr(x, "ndim", 0) == 2 else 0
+        if (out is None and not streamed and not graph and chunk is None and copy_streams == 1 and run_streams == 1
+                and 0 < rows <= PredStepPipeline.MAX_ROWS and not (isinstance(x, torch.Tensor) and x.is_pinned())):
+            # the planner's call (pred_step): a few queries, the caller waits -- one captured graph per batch size
+            key = ("pred", str(device))
+            if key not in self._const:
+                self._const[key] = PredStepPipeline(device, self.in_features, self.out_features)
+            return self._const[key].run(x, lambda xs, ys: ops.forward(xs, centers, log_sigs, kernel, bias, gd=gd,
+                                                                      basis=self._basis, out=ys),
+                                        (centers.data_ptr(), log_sigs.data_ptr(), kernel.data_ptr(), bias.data_ptr()))
         if streamed and (self.out_features > 16 or not ops.upload_streamed_available()):
             streamed = False
         if streamed == "auto":

@@ -57,3 +57,29 @@ for name in ("c1_cartesian_1x1000", "c2_frenet_12x100", "c2b_frenet_1x1000_o10")
         y0 = ops.forward(x, c, ls, W, b, gd=gd, basis=basis, split=False)
         err = float((y_ref - y0).abs().max() / y0.abs().max().clamp_min(1e-30))
         print("%-24s B=%6d  eager %6.1f us  graph %6.2f us/call   split-vs-unsplit %.1e" % (name, B, t_eager, t_graph, err))
+    if name == "c2_frenet_12x100" and not PROFILE:
+        # the planner's call: module.apply on a NumPy batch, wall clock (the call waits for its result)
+        import time
+        from irbfn_b200.basis import gaussian
+        from irbfn_b200.model import WCRBFNet, device_params
+        net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                       cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"], cfg["delta"])
+        dp = device_params({"params": {"rbf_list": {"centers": z["p/rbf_list/centers"], "log_sigs": z["p/rbf_list/log_sigs"]},
+                                       "linear": {"kernel": z["p/linear/kernel"], "bias": z["p/linear/bias"]}}}, dev)
+        for B in (1, 400, 4096):
+            xn = np.tile(xs, (4, 1))[:B].astype(np.float64)
+            for _ in range(20):
+                net.apply(dp, xn)
+            t0 = time.perf_counter()
+            for _ in range(300):
+                net.apply(dp, xn)
+            t_new = (time.perf_counter() - t0) / 300 * 1e6
+            old = lambda: net.apply_host(dp, xn, chunk=148 * 1024)      # the chunk pipeline (what apply did before)
+            for _ in range(20):
+                old()
+            t0 = time.perf_counter()
+            for _ in range(300):
+                old()
+            t_old = (time.perf_counter() - t0) / 300 * 1e6
+            print("module.apply(NumPy float64 x), B=%5d: %6.1f us per call, chunk pipeline %6.1f us (wall clock, result "
+                  "on the host)" % (B, t_new, t_old))

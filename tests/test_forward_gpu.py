@@ -337,6 +337,43 @@ def test_host_pipeline_variants_agree(cuda_device):
     assert np.array_equal(net.apply_host(dp, x * 0.5, chunk=2048), yh.numpy())
 
 
+def test_pred_step_sized_host_calls_replay_one_graph(cuda_device):
+    """module.apply on a small NumPy batch (the planner's pred_step, irbfn_planner.py:29-32; float64 states): upload,
+    latency kernel and download captured once per batch size (hostpath.PredStepPipeline).  First call (eager + capture),
+    replays with new values, parameters updated in place, and a batch beyond the staging buffers (chunk pipeline)."""
+    import os
+    from conftest import GOLDEN_DIR
+    from irbfn_b200.basis import gaussian
+    from irbfn_b200.hostpath import PredStepPipeline
+    from irbfn_b200.model import WCRBFNet, device_params
+    cfg, params, arr = load_golden(os.path.join(GOLDEN_DIR, "c2_frenet_12x100.npz"))
+    net = WCRBFNet(cfg["in_features"], cfg["out_features"], cfg["num_kernels"], gaussian, cfg["num_regions"],
+                   cfg["lower_bounds"], cfg["upper_bounds"], cfg["dimension_ranges"], cfg["activation_idx"],
+                   cfg["delta"])
+    dp = device_params({"params": params}, cuda_device)
+    x_all = np.tile(arr["x"].astype(np.float64), (5, 1))
+    ref = lambda xx, pp: orc.wcrbf_forward(xx.astype(np.float32).astype(np.float64), pp, cfg)
+    for B in (1, 400, 4096, 1):
+        for rep in range(3):                                   # capture, replay, replay -- new values every time
+            x = x_all[rep * 7: rep * 7 + B] * (1.0 - 0.05 * rep)
+            y = net.apply(dp, x)
+            assert isinstance(y, np.ndarray) and y.shape == (B, cfg["out_features"]) and y.dtype == np.float32
+            assert rel_max(y, ref(x, params)) < OUT_TOL, (B, rep)
+    pipe = net._const[("pred", str(torch.device(cuda_device)))]
+    assert isinstance(pipe, PredStepPipeline) and len(pipe._graphs) == 3
+    # parameters updated in place (same buffers): the captured launch reads the new values
+    dp["params"]["linear"]["bias"].add_(0.25)
+    y = net.apply(dp, x_all[:400])
+    p2 = {k: dict(v) for k, v in params.items()}
+    p2["linear"]["bias"] = np.asarray(params["linear"]["bias"]) + 0.25
+    assert rel_max(y, ref(x_all[:400], p2)) < OUT_TOL
+    dp["params"]["linear"]["bias"].sub_(0.25)
+    # one row more than the staging buffers hold: the chunk pipeline
+    y = net.apply(dp, x_all[:4097])
+    assert y.shape == (4097, cfg["out_features"]) and rel_max(y, ref(x_all[:4097], params)) < OUT_TOL
+    assert len(pipe._graphs) == 3
+
+
 def test_streamed_host_path_matches_the_device_resident_forward(cuda_device):
     """irbfn_forward_streamed through apply_host: ONE launch whose query tiles wait for their chunk of the upload and
     which stores y straight into pinned host memory.  Bit-identical to the unsplit device-resident forward; calling it
