@@ -388,6 +388,11 @@ def main():
                 "c5_fwd_ms_gate_sparse": r4(c5.get("fwd_gate_sparse_ms_per_2p24")),
                 "c5_fwd_vjp_ms_per_2p22": r4(c5.get("fwd_vjp_ms_per_2p22")),
                 "c5_fwd_vjp_ms_gate_sparse": r4(c5.get("fwd_vjp_gate_sparse_ms_per_2p22"))}
+            pr = (out.get("extras") or {}).get("pred_step_latency") or {}
+            out["summary"].update({"pred_step_b1_us_graph": r4(pr.get("kernel_us_in_cuda_graph_B1")),
+                                   "pred_step_b1_us_apply_numpy": r4(pr.get("module_apply_numpy_us_wall_B1")),
+                                   "pred_step_b400_us_graph": r4(pr.get("kernel_us_in_cuda_graph_B400")),
+                                   "pred_step_b400_us_apply_numpy": r4(pr.get("module_apply_numpy_us_wall_B400"))})
         emit(out)
     elif not args.no_extras:
         extras(net, params, cfg, dev, world, args)   # collectives inside: every rank takes part
@@ -619,6 +624,34 @@ def extras(net, params, cfg, dev, world, args):
                                             "note": "irbfn_vs_explicit_frenet.ipynb cells 8-13 on one device"}
     del etab
     del tabx, taby, tab_
+
+    # pred_step (src/irbfn_mpc/irbfn_planner.py:29-32): the planner evaluates ONE state per control step, the
+    # notebooks 400.  (a) the kernel alone, replayed from a CUDA graph (irbfn_forward_path: the pair-parallel latency
+    # kernel, one launch); (b) module.apply on a NumPy float64 batch, wall clock of the whole call with the result
+    # back on the host (upload + kernel + download replayed as one captured graph per batch size).
+    pred = {"shape": "C2 R12_K100_D8_O2", "path": {}}
+    for Bp in (1, 400):
+        xp = x4[:Bp].contiguous()
+        yp = torch.empty((Bp, O), device=dev)
+        fwd_p = lambda: ops.forward(xp, p["rbf_list"]["centers"], p["rbf_list"]["log_sigs"], p["linear"]["kernel"],
+                                    p["linear"]["bias"], gd=net._gate_pack(dev), basis=0, out=yp)
+        gp_, sp_ = torch.cuda.CUDAGraph(), torch.cuda.Stream(dev)
+        with torch.cuda.stream(sp_):
+            fwd_p()
+            with torch.cuda.graph(gp_, stream=sp_):
+                for _ in range(20):
+                    fwd_p()
+        torch.cuda.synchronize()
+        pred["path"]["B%d" % Bp] = ops.forward_path(Bp, R, K, D, O)
+        pred["kernel_us_in_cuda_graph_B%d" % Bp] = timed(gp_.replay, 20, 3) / 20 * 1e3
+        xn = xp.cpu().numpy().astype(np.float64)
+        for _ in range(20):
+            net.apply(params, xn)
+        t0 = time.perf_counter()
+        for _ in range(200):
+            net.apply(params, xn)
+        pred["module_apply_numpy_us_wall_B%d" % Bp] = (time.perf_counter() - t0) / 200 * 1e6
+    res["pred_step_latency"] = pred
     if not args.no_other:
         other = other_configs(dev, world, args, timed)
         tail["c5"] = other.pop("c5_summary")
