@@ -90,6 +90,6 @@ if __name__ == "__main__":
     tag = sys.argv[1]
     os.makedirs(PR, exist_ok=True)
     launches(tag)
-    for kind in ("fwd", "bwdp", "bwdx", "jac", "nearest", "bwdps", "bwdxs"):
+    for kind in ("fwd", "bwdp", "bwdx", "jac", "nearest", "bwdps", "bwdxs", "fwdsmall"):
         report(kind, tag)
     print(sorted(os.listdir(PR)))
