@@ -80,6 +80,25 @@ def test_argument_validation_happens_before_any_device_work():
     assert b"unknown" in lib.irbfn_error_string(-99)
 
 
+def test_forward_path_is_a_host_side_decision():
+    """irbfn_forward_path (no device needed): the planner's batch sizes take the latency kernel, shard-sized batches
+    the split kernel, the lattice the tiled one; asking for more than y, wide outputs or a large parameter set keeps
+    the throughput kernels; bad dimensions are rejected."""
+    lib = _lib.load()
+    path = lib.irbfn_forward_path
+    C2 = (12, 100, 8, 2)
+    assert [path(B, *C2, 1) for B in (1, 400, 4096, 4369)] == [_lib.PATH_SMALL] * 4
+    assert path(4370, *C2, 1) == _lib.PATH_SPLIT and path(32768, *C2, 1) == _lib.PATH_SPLIT
+    assert path(1 << 20, *C2, 1) == _lib.PATH_TILED
+    assert path(1, *C2, 0) == _lib.PATH_SPLIT                      # hidden activations / gate output wanted
+    assert path(1, 12, 100, 8, 18, 1) == _lib.PATH_SPLIT           # more than one output window
+    assert path(1, 64, 4096, 6, 16, 1) == _lib.PATH_SPLIT          # C5: 7.6 MB of parameters per CTA would not do
+    assert path(1, 1, 2, 4, 1, 1) == _lib.PATH_SMALL               # a single kernel tile cannot be split anyway
+    assert path(0, *C2, 1) == -1 and path(4, 12, 100, 9, 2, 1) == -1
+    # the small path needs no workspace, whatever irbfn_forward_workspace_bytes offers for the split one
+    assert lib.irbfn_forward_workspace_bytes(400, *C2, 1) > 0
+
+
 def test_backward_argument_validation():
     lib = _lib.load()
     one = C.c_void_p(16)
