@@ -13,8 +13,8 @@ constexpr int kFwdTQ = 1024;  // queries per CTA tile of the 256-thread kernels 
 // floats of one transposed 4-kernel tile: rows -c_0..-c_{D-1} and the width scales
 inline int fwd_tile_floats(int D) { return (D + 1) * 4; }
 
-// Threads per CTA of the forward kernel: 512 (<= 128 registers per thread) while the output
-// accumulators are small, 256 for the wide output windows.
+// Threads per CTA of the forward kernel: 256 for every output window (the one compiled CTA size; 512-thread CTAs at
+// <= 128 registers per thread were measured slower in round 1).
 inline int fwd_threads_for(int OT) { (void)OT; return 256; }
 
 // Compiled output-window widths of the forward kernel.
