@@ -213,7 +213,17 @@ class _IrbfnModule:
                 raise KeyError("params have no rbf_list/log_sigs and the module is not fixed_width")
             log_sigs = self._fixed("log_sigs", device)
         if self._ls_shift != 0.0:
-            log_sigs = log_sigs + self._ls_shift     # gaussian_wide / _wider on the gaussian kernel (basis.py)
+            # gaussian_wide / _wider on the gaussian kernel (basis.py).  The shifted widths are kept until the source
+            # tensor is replaced or written to (its version counter), so repeated calls on a device-resident tree
+            # launch no extra kernel and hand the same buffer to captured graphs (hostpath: graph keys are addresses).
+            if log_sigs.requires_grad:
+                return centers, log_sigs + self._ls_shift        # autograd needs the fresh node
+            key = ("ls_shift", str(device))
+            hit = self._const.get(key)
+            # the entry holds the source tensor itself (identity, not address: a freed tensor's address is reused)
+            if hit is None or hit[0] is not log_sigs or hit[1] != log_sigs._version:
+                self._const[key] = hit = (log_sigs, log_sigs._version, log_sigs + self._ls_shift)
+            log_sigs = hit[2]
         return centers, log_sigs
 
     # ---- init: same tree, shapes and distributions as the reference -------------------------
