@@ -339,7 +339,7 @@ def test_host_pipeline_variants_agree(cuda_device):
 
 def test_pred_step_sized_host_calls_replay_one_graph(cuda_device):
     """module.apply on a small NumPy batch (the planner's pred_step, irbfn_planner.py:29-32; float64 states): upload,
-    latency kernel and download captured once per batch size (hostpath.PredStepPipeline).  First call (eager + capture),
+    latency kernel and download captured once per batch size (hostpath.PredStepPipeline).  First calls (eager, capture),
     replays with new values, parameters updated in place, and a batch beyond the staging buffers (chunk pipeline)."""
     import os
     from conftest import GOLDEN_DIR
@@ -354,7 +354,7 @@ def test_pred_step_sized_host_calls_replay_one_graph(cuda_device):
     x_all = np.tile(arr["x"].astype(np.float64), (5, 1))
     ref = lambda xx, pp: orc.wcrbf_forward(xx.astype(np.float32).astype(np.float64), pp, cfg)
     for B in (1, 400, 4096, 1):
-        for rep in range(3):                                   # capture, replay, replay -- new values every time
+        for rep in range(4):                                   # eager, eager + capture, replay, replay -- new values every time
             x = x_all[rep * 7: rep * 7 + B] * (1.0 - 0.05 * rep)
             y = net.apply(dp, x)
             assert isinstance(y, np.ndarray) and y.shape == (B, cfg["out_features"]) and y.dtype == np.float32
