@@ -36,6 +36,18 @@ def test_every_declared_symbol_is_exported():
         assert getattr(lib, name) is not None
 
 
+def test_every_declared_symbol_has_a_row_in_integration_md():
+    """INTEGRATION.md section 0 names the reference interface each entry point replaces; a symbol added to the header
+    without a row there fails here (suffix forms like "(+ `_workspace_bytes`)" count for their base symbol)."""
+    src = open(HEADER).read()
+    doc = open(os.path.join(os.path.dirname(HEADER), "..", "INTEGRATION.md")).read()
+    syms = sorted(set(re.findall(r"\b(irbfn_[a-z0-9_]+)\s*\(", src)))
+    suffixes = ("_workspace_bytes", "_available", "_max_n", "_buffer_bytes")
+    missing = [x for x in syms if x not in doc
+               and not any(x.endswith(suf) and x[: -len(suf)] in doc and suf in doc for suf in suffixes)]
+    assert not missing, missing
+
+
 def test_header_constants_match_binding():
     src = open(HEADER).read()
     val = lambda name: int(re.search(r"#define\s+%s\s+\(?(-?\w+)\)?" % name, src).group(1).rstrip("u"), 0)
